@@ -22,7 +22,11 @@ struct output_dumper {
     explicit output_dumper(std::ostream& o) : out(o) {}
 
     template <typename T, typename U, typename E>
-    void operator()(size_t idx, dlib::add_layer<T, U, E>& l) const { ref_io::write_tensor(out, static_cast<int>(idx), l.get_output()); }
+    void operator()(size_t idx, dlib::add_layer<T, U, E>& l) const
+    {
+        // layers under an in-place layer (affine_) refuse get_output() (core.h:1102-1109): skip them
+        try { ref_io::write_tensor(out, static_cast<int>(idx), l.get_output()); } catch (const std::exception&) {}
+    }
 
     template <typename T>
     void operator()(size_t, T&) const {}
