@@ -1,0 +1,60 @@
+// Static execution plan of net_type / anet_type for the engine: the reference's 231-layer template
+// graph (NetStructure.h:172-299, executor semantics dnn/core.h:932-948,998-1009) is folded into 49
+// "conv groups" (conv [+ max-pool in front] [+ mish / bn|affine behind]) that read and write channel
+// slices of ONE activation buffer per resolution level, so that no concat / tag layer ever copies
+// (SURVEY §2.3 "concat: eliminated").
+//
+// Physical channel order inside a level buffer = reverse creation order of the tensors living at
+// that resolution ("newest first").  With that order every conv group's input -- whatever
+// concat_prev_/concat_ chain produced it (layers.h:2425-2455,3652-3667) -- is one contiguous channel
+// range; where dlib's logical channel order differs from the physical one (concat2/concat3 list
+// their tags oldest first) the group's filters are permuted along Cin when they are loaded.
+#pragma once
+#include "net_model.h"
+
+namespace ab {
+
+struct ConvGroup {
+    int dlib_conv = -1;   // layer<i> of the con_/cont_
+    int dlib_bn = -1;     // layer<i> of its bn_/affine_ (-1: none, the class head and the `up` conts)
+    bool has_mish = false;
+    bool bn_first = false;  // conv -> bn -> mish (level0, level0t) instead of conv -> mish -> bn (dense / down)
+    bool is_cont = false;
+    int ksize = 3, stride = 1, pad = 1;
+    bool pool_input = false;  // max_pool 3x3/2 in front (transition_down)
+    bool dead = false;        // output never consumed
+    int in_level = 0;         // resolution level of the input slice; -1: the image tensor
+    int in_c0 = 0, cin = 0;
+    std::vector<int> perm;    // perm[logical ci] = physical ci (relative to in_c0)
+    int out_level = 0;        // -2: logits
+    int out_c0 = 0, cout = 0; // for dead groups: offset into the dead-scratch buffer (always 0)
+    // offsets (floats) into the flat parameter arena
+    size_t w_off = 0, b_off = 0, bn_off = 0;
+    size_t nweights() const { return (size_t)cout * cin * ksize * ksize; }
+};
+
+struct Plan {
+    int levels = 6;
+    int class_count = 0;
+    std::vector<ConvGroup> groups;        // forward order
+    std::vector<int> level_channels;      // channels of the activation buffer of each level (0..levels)
+    int max_dead_channels = 0;
+    size_t num_params = 0;                // floats in the arena
+    // per dlib layer index: arena offset and size of its params tensor (con/cont/bn/affine), else size 0
+    std::vector<size_t> layer_off, layer_size;
+};
+
+Plan build_plan(const NetModel& net);
+
+// spatial size of each level for an h x w input: level 0 = input size, level n = 1+(level n-1 - 3)/2
+// (max_pool_<3,3,2,2>, layers.h:994-1012).  Also checks that the `up` path lands on the skip sizes
+// (cont_ out = 2*in+1, layers.h:521-535), i.e. h,w are "canonical" 64k+63 -- other sizes would need
+// concat_prev_'s +-1 bilinear resize (layers.h:2494-2521), which this build rejects.
+struct LevelDims { int h[8], w[8]; };
+LevelDims level_dims(int h, int w, int levels);
+
+// dlib layout <-> arena layout for one group's filters (permutation along Cin)
+void pack_filters(const ConvGroup& g, const float* dlib_params, float* arena_w, float* arena_b);
+void unpack_filters(const ConvGroup& g, const float* arena_w, const float* arena_b, float* dlib_params);
+
+}  // namespace ab

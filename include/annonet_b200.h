@@ -1,0 +1,176 @@
+/* annonet_b200 -- C ABI of the B200-native engine for annonet's segmentation CNN.
+ *
+ * This is the drop-in boundary: plain C, caller-owned buffers, int status
+ * codes.  Each entry point names the reference interface it replaces; paths are relative to
+ * the reference checkout (reunanen/annonet).  The reference-side binding (a replacement
+ * NetPimpl.cpp that keeps dlib-dnn-pimpl-wrapper/NetPimpl.h unchanged) is shown in
+ * INTEGRATION.md and shipped as shim/NetPimpl_b200.cpp.
+ *
+ * There is no CPU fallback: every compute entry point needs a CUDA device (sm_100a) and
+ * returns AB_ERR_CUDA otherwise.
+ */
+#ifndef ANNONET_B200_H
+#define ANNONET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ab_net ab_net;
+
+typedef enum {
+    AB_OK = 0,
+    AB_ERR_ARGUMENT = 1,      /* std::invalid_argument / DLIB_CASSERT in the reference            */
+    AB_ERR_SERIALIZATION = 2, /* dlib::serialization_error                                        */
+    AB_ERR_CUDA = 3,          /* dlib::cuda_error (incl. out of memory -> process exit code != 0) */
+    AB_ERR_STATE = 4,         /* call order violated (e.g. training a runtime net)                */
+    AB_ERR_TOO_LARGE = 5      /* std::runtime_error of GetRecommendedInputDimension               */
+} ab_status;
+
+/* precision of activations/weights inside the convolutions; accumulation is always fp32 */
+typedef enum {
+    AB_PRECISION_FP32 = 0, /* fp32 FMA path: logits within 1e-4 relative of the dlib CPU build */
+    AB_PRECISION_BF16 = 1  /* bf16 tcgen05 path: within 2e-2                                    */
+} ab_precision;
+
+/* dlib::loss_multiclass_log_per_pixel_weighted_::weighted_label<uint16_t>
+ * (dlib/dlib/dnn/weighted_label.h:8-20): identical memory layout, 8 bytes. */
+typedef struct {
+    uint16_t label;
+    float weight;
+} ab_wlabel;
+
+/* inclusive rectangles, as tiling::dlib_tile (tiling/dlib-wrapper.h:11-16) */
+typedef struct {
+    int32_t full[4];            /* left, top, right, bottom */
+    int32_t non_overlapping[4];
+    int32_t unique[4];
+} ab_tile;
+
+typedef struct {
+    int32_t levels;          /* DLIB_DNN_PIMPL_WRAPPER_LEVEL_COUNT (NetStructure.h:103-108); 6 */
+    int32_t class_count;     /* num_filters of layer<1> (NetPimpl.cpp:37-41)                   */
+    int32_t is_training_net; /* 1: net_type (bn_), 0: anet_type (affine_)                      */
+    int32_t precision;
+    int64_t num_params;      /* floats in all parameter tensors                                */
+    int32_t num_layers;      /* dlib layer count incl. loss and input: 231                     */
+    int32_t device;
+} ab_net_info_t;
+
+typedef enum {
+    AB_HYPER_LEARNING_RATE = 0,          /* TrainingNet::SetLearningRate                  NetPimpl.cpp:43-46   */
+    AB_HYPER_WEIGHT_DECAY = 1,           /* dlib::sgd(weight_decay, momentum)             NetPimpl.h:21-22     */
+    AB_HYPER_MOMENTUM = 2,
+    AB_HYPER_BN_STATS_WINDOW = 3,        /* SetAllBatchNormalizationRunningStatsWindowSizes NetPimpl.cpp:58-61 */
+    AB_HYPER_LR_SHRINK_FACTOR = 4,       /* SetLearningRateShrinkFactor                   NetPimpl.cpp:63-66   */
+    AB_HYPER_ITERS_WITHOUT_PROGRESS = 5, /* SetIterationsWithoutProgressThreshold         NetPimpl.cpp:48-51   */
+    AB_HYPER_SOLVER = 6,                 /* 0 = sgd (compiled-in default), 1 = adam (NetPimpl.h:17-23)        */
+    AB_HYPER_ADAM_BETA1 = 7,
+    AB_HYPER_ADAM_BETA2 = 8,
+    AB_HYPER_SKIP_DEAD_LAYERS = 9        /* 1: do not run the 7 never-consumed dense layers in training        */
+} ab_hyper_id;
+
+/* ---- library ------------------------------------------------------------------------------ */
+const char* ab_version(void);
+/* message of the last failing call on this thread (the what() of the C++ exception the shim rethrows) */
+const char* ab_last_error(void);
+void ab_free(void* p);
+
+/* ---- net lifetime: NetPimpl::TrainingNet / RuntimeNet constructors, NetPimpl.cpp:18-26,200-224 */
+ab_status ab_net_create(int device, int precision, ab_net** out);
+void ab_net_destroy(ab_net* net);
+/* RuntimeNet copy constructor / operator= (deep copy of the weights), NetPimpl.cpp:210-224 */
+ab_status ab_net_clone(const ab_net* net, ab_net** out);
+ab_status ab_net_info(const ab_net* net, ab_net_info_t* info);
+
+/* TrainingNet::Initialize + SetNetWidth + SetClassCount (annonet_train_main.cpp:401-405) followed by
+ * the parameter allocation dlib does on the first forward pass (layers.h:170-193, Glorot uniform). */
+ab_status ab_net_init_random(ab_net* net, int class_count, double width_scaler, int min_filter_count, uint64_t seed);
+
+/* {Training,Runtime}Net::Deserialize (NetPimpl.cpp:170-198,305-320): a dlib stream of net_type
+ * (bn_con2 records) or anet_type (affine_ records); which one is detected from the records. */
+ab_status ab_net_load_dlib(ab_net* net, const void* bytes, size_t n);
+/* {Training,Runtime}Net::Serialize.  as_runtime=1 on a training net performs
+ * RuntimeNet::operator=(TrainingNet) (NetPimpl.cpp:226-232): bn_ -> affine_ with the running
+ * statistics folded in (layers.h:2144-2163).  *bytes is released with ab_free. */
+ab_status ab_net_save_dlib(ab_net* net, int as_runtime, void** bytes, size_t* n);
+
+/* ---- sizes: NetPimpl.cpp:137-146,246-285 --------------------------------------------------- */
+int ab_required_input_dimension(void);
+ab_status ab_recommended_input_dimension(int minimum, int* out);
+
+/* ---- inference ---------------------------------------------------------------------------- */
+/* RuntimeNet::Forward (NetPimpl.cpp:292-298): u8 HWC image (channels = 3) -> logits, NCHW f32
+ * [class_count][h][w] written to logits_host (may be NULL: result stays on the device). */
+ab_status ab_forward(ab_net* net, const uint8_t* image_hwc, int h, int w, float* logits_host);
+/* RuntimeNet::operator() / Process (NetPimpl.cpp:287-290): Forward + to_label with gains
+ * (loss.h:2921-2969). gains may be NULL (ngains = 0). */
+ab_status ab_process(ab_net* net, const uint8_t* image_hwc, int h, int w, const double* gains, int ngains,
+                     uint16_t* labels_host);
+
+/* tiling::get_tiles (tiling/tiling.cpp:23-87, dlib-wrapper.h:27-39).  Writes at most cap tiles,
+ * *count receives the total. */
+ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, int overlap_x, int overlap_y,
+                       ab_tile* out, int cap, int* count);
+
+/* annonet_infer() (annonet_infer.cpp:32-185, without the detection-level blob filter): tiles ->
+ * enlarge to 64w+63 -> clamp-to-edge fill -> forward -> blend -> argmax(+gain), all on the device.
+ * rank/world shard the tile list (tile i belongs to rank i % world); with world > 1 each caller
+ * receives labels only where its own tiles' unique rectangles... see ab_infer_tiled_merge.
+ * labels_host: h*w uint16.  blended_host (optional): class_count*h*w f32 (temp.blended_output). */
+ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, int max_tile_w, int max_tile_h,
+                         const double* gains, int ngains, uint16_t* labels_host, float* blended_host);
+/* Same with image and labels resident in device memory (image_dev: h*w*3 u8, labels_dev: h*w u16). */
+ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,
+                                const double* gains, int ngains, void* labels_dev);
+/* Multi-GPU inference: this rank runs the tiles of rows  row % world == rank  of the
+ * tile grid into its private blend canvas; canvases are summed by the caller's collective
+ * (NCCL all-reduce on the pointer returned here) before ab_infer_finish runs the argmax. */
+ab_status ab_infer_tiled_partial(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,
+                                 int rank, int world, void** canvas_dev, size_t* canvas_floats);
+ab_status ab_infer_finish(ab_net* net, int h, int w, const double* gains, int ngains, void* labels_dev);
+
+/* ---- training ----------------------------------------------------------------------------- */
+ab_status ab_set_hyper(ab_net* net, int id, double value);
+ab_status ab_get_hyper(ab_net* net, int id, double* value);
+
+/* TrainingNet::StartTraining (NetPimpl.cpp:148-151 -> dnn_trainer::train_one_step,
+ * trainer.h:197-224): n crops of h x w, images n*h*w*3 u8, labels n*h*w ab_wlabel.  Returns once
+ * the inputs are staged and the step is enqueued on the net's stream (depth-1 asynchrony). */
+ab_status ab_train_step_async(ab_net* net, const uint8_t* images, const ab_wlabel* labels, int n, int h, int w);
+/* Same with inputs already in device memory. */
+ab_status ab_train_step_device(ab_net* net, const void* images_dev, const void* labels_dev, int n, int h, int w);
+/* Blocks until the enqueued step is finished (dnn_trainer::get_net / wait_for_thread_to_pause,
+ * trainer.h:143-151,882-885); *loss = loss of the last step (trainer.h:751-754). */
+ab_status ab_train_sync(ab_net* net, double* loss);
+/* add_loss_layer::compute_parameter_gradients (core.h:2570-2580): forward + loss + backward, no update. */
+ab_status ab_compute_gradients(ab_net* net, const uint8_t* images, const ab_wlabel* labels, int n, int h, int w,
+                               double* loss);
+/* training-mode logits of the last step, NCHW f32 [n][class_count][h][w] */
+ab_status ab_get_logits(ab_net* net, float* out, size_t capacity_floats);
+/* parameter gradients of one dlib layer<idx> in dlib's layout (visit_layer_parameter_gradients, core.h:3806-3816) */
+ab_status ab_get_layer_gradient(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
+ab_status ab_get_layer_params(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
+
+/* data-parallel training: flat gradient arena for the caller's/engine's all-reduce
+ * (multi_device_tensor_averager, tensor_tools.h:1609-1736 -> NCCL) */
+ab_status ab_gradient_arena(ab_net* net, void** grads_dev, size_t* count_floats);
+/* NCCL communicator owned by the engine: id = 128-byte ncclUniqueId produced on rank 0 */
+ab_status ab_comm_unique_id(void* id128);
+ab_status ab_comm_init(ab_net* net, const void* id128, int rank, int world);
+
+/* set_weights (annonet_train.h:20-83): per-pixel loss weights from a u16 label crop (host function) */
+ab_status ab_set_weights(const uint16_t* labels, int h, int w, double class_weight, double image_weight, float* weights_out);
+
+/* ---- instrumentation ---------------------------------------------------------------------- */
+void* ab_stream(ab_net* net);              /* cudaStream_t the engine launches on */
+uint64_t ab_kernel_launches(ab_net* net);   /* kernels of this library launched so far on this net */
+ab_status ab_device_synchronize(ab_net* net);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ANNONET_B200_H */
