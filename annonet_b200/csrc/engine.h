@@ -1,0 +1,138 @@
+// The engine behind the C ABI: owns the device-resident parameters of one net (net_type or
+// anet_type), the static plan, and the activation workspaces; sequences the kernels of
+//   * RuntimeNet::Forward / annonet_infer()            (dnn/core.h:932-948, annonet_infer.cpp:32-185)
+//   * dnn_trainer's step: forward, loss, backward, update (trainer.h:631-671,743-828; core.h:998-1023)
+// on one CUDA stream (plus a side stream for the NCCL gradient all-reduce).
+#pragma once
+#include "kernels.h"
+#include "net_model.h"
+#include "plan.h"
+
+#include <cuda_runtime.h>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace ab {
+
+struct cuda_error : std::runtime_error { using std::runtime_error::runtime_error; };
+struct state_error : std::runtime_error { using std::runtime_error::runtime_error; };
+
+void cuda_check(cudaError_t e, const char* what, const char* file, int line);
+#define AB_CUDA(x) ::ab::cuda_check((x), #x, __FILE__, __LINE__)
+
+// cudaMalloc'ed block with RAII
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    void release();
+    void reserve(size_t n);  // grows (never shrinks); contents are lost on growth
+    template <typename T> T* as() const { return (T*)p; }
+};
+
+struct Hyper {
+    double learning_rate = 1e-2;   // dnn_trainer default (trainer.h:78)
+    double weight_decay = 0.001;   // NetPimpl.h:22
+    double momentum = 0.9;
+    double lr_shrink_factor = 0.1;
+    double iters_without_progress = 2000;
+    int solver = 0;                // 0 sgd, 1 adam
+    double adam_beta1 = 0.9, adam_beta2 = 0.999;
+    int skip_dead_layers = 0;
+};
+
+struct NcclApi;
+
+class Engine {
+public:
+    Engine(int device, int precision);
+    ~Engine();
+
+    void load(const NetModel& m);
+    NetModel snapshot(bool as_runtime);
+    bool loaded() const { return loaded_; }
+    bool is_training() const { return model_.is_training; }
+    const Plan& plan() const { return plan_; }
+    const NetModel& model() const { return model_; }
+    int device() const { return device_; }
+    int precision() const { return precision_; }
+    cudaStream_t stream() const { return stream_; }
+    void synchronize();
+
+    // ---- inference (runtime nets) ----
+    // one image already on the device as u8 HWC; returns device logits [K][h][w] (valid until the next call)
+    const float* forward_device(const uint8_t* img_dev, int h, int w);
+    const float* forward_host(const uint8_t* img_host, int h, int w);
+    void process_host(const uint8_t* img_host, int h, int w, const double* gains, int ngains, uint16_t* labels_host);
+    // annonet_infer(); image/labels on the device.  rank/world select tile rows (world = 1: all tiles)
+    void infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, int rank, int world);
+    void infer_finish_device(int h, int w, const double* gains, int ngains, uint16_t* labels_dev);
+    float* canvas() const { return canvas_.as<float>(); }
+    void infer_tiled_host(const uint8_t* img_host, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
+                          uint16_t* labels_host, float* blended_host);
+
+    // ---- training (training nets) ----
+    Hyper hyper;
+    void set_bn_window(unsigned long long w);
+    void train_step_device(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
+    void train_step_host(const uint8_t* imgs, const void* labels, int n, int h, int w, bool update);
+    double train_sync();  // waits; returns the loss of the last step
+    const float* train_logits() const { return t_logits_.as<float>(); }
+    int last_n() const { return tn_; } int last_h() const { return th_; } int last_w() const { return tw_; }
+    float* grads() const { return grads_.as<float>(); }
+    float* params() const { return params_.as<float>(); }
+    void layer_values(int dlib_layer, bool gradient, std::vector<float>& out);  // dlib layout
+
+    void comm_init(const void* id128, int rank, int world);
+    int world() const { return world_; }
+
+private:
+    // workspaces
+    struct Levels { DevBuf buf[8]; LevelDims dims; int n = 0, h = 0, w = 0; };
+    void ensure_infer_ws(int h, int w);
+    void ensure_train_ws(int n, int h, int w);
+    void run_inference_graph(int h, int w);
+    void forward_train(int n, int h, int w);
+    void backward_train(int n, int h, int w);
+    void optimizer_step();
+    void allreduce_range(size_t lo, size_t hi);
+    k::Slice level_slice(Levels& L, int level, int c0, int C) const;
+
+    int device_, precision_;
+    cudaStream_t stream_ = nullptr, comm_stream_ = nullptr;
+    cudaEvent_t ev_bucket_[8] = {}, ev_comm_done_ = nullptr, ev_stage_ = nullptr;
+    bool loaded_ = false;
+    NetModel model_;  // host copy of the structure (+ parameters as loaded; device is authoritative after load)
+    Plan plan_;
+
+    DevBuf params_, grads_, mom_, adam_v_, lr_mul_, wd_mul_, running_;  // running_: per bn group [mean(C) | var(C)]
+    std::vector<size_t> running_off_;   // per group
+    std::vector<unsigned long long> num_updates_, window_;  // per group
+    unsigned long long adam_t_ = 0;
+
+    // inference workspace
+    Levels iw_;
+    DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_;
+    void* pinned_ = nullptr; size_t pinned_bytes_ = 0;
+    void* pinned(size_t bytes);
+
+    // training workspace
+    Levels tw_act_, tw_grad_;
+    DevBuf t_x_, t_logits_, t_glogits_, t_z_, t_pool_, t_dz_, t_dpool_, t_dead_, t_stats_, t_sums_, t_scratch_, t_imgs_, t_labels_,
+        t_loss_;
+    std::vector<size_t> z_off_, pool_off_, stats_off_;
+    int tn_ = 0, th_ = 0, tw_ = 0;
+    bool stats_valid_ = false;
+    double* loss_host_ = nullptr;  // pinned
+
+    // data parallel
+    std::unique_ptr<NcclApi> nccl_;
+    void* comm_ = nullptr;
+    int rank_ = 0, world_ = 1;
+};
+
+}  // namespace ab

@@ -1,0 +1,57 @@
+// Shared device helpers of the fp32 kernels.
+#pragma once
+#include "kernels.h"
+
+#include <atomic>
+
+namespace ab {
+namespace k {
+
+extern std::atomic<unsigned long long> g_launches;  // kernels of this library launched so far
+inline void count_launch(int n = 1) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+constexpr int kNumSMs = 148;
+
+// mish_: y = x - 2x/(e^2 + 2e + 2), e = exp(x)   (cpu_dlib.cpp:1510-1523; fp32 exp overflow -> y = x)
+__device__ __forceinline__ float mish_f(float x)
+{
+    const float e = expf(x);
+    const float delta = 2.f * e + e * e + 2.f;
+    return x - 2.f * x / delta;
+}
+
+// d mish / dx with dlib's clamps (cpu_dlib.cpp:1531-1543)
+__device__ __forceinline__ float mish_grad_f(float x)
+{
+    if (x >= 8.f) return 1.f;
+    if (x <= -8.f) return 0.f;
+    const float e = expf(x);
+    const float delta = 2.f * e + e * e + 2.f;
+    const float omega = 4.f * (x + 1.f) + 4.f * e * e + e * e * e + e * (4.f * x + 6.f);
+    return e * omega / (delta * delta);
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ const float* plane(const Slice& s, int n, int c, long long hw)
+{
+    return s.p + (long long)n * s.sstride + (long long)(s.c0 + c) * hw;
+}
+__device__ __forceinline__ float* plane_w(const Slice& s, int n, int c, long long hw)
+{
+    return s.p + (long long)n * s.sstride + (long long)(s.c0 + c) * hw;
+}
+
+}  // namespace k
+}  // namespace ab

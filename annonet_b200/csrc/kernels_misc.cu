@@ -1,0 +1,211 @@
+// Input conversion, loss, label maps, tile blending and the optimizer: coalesced HBM-bound kernels.
+#include "kcommon.cuh"
+
+namespace ab {
+namespace k {
+namespace {
+
+// input_rgb_image::to_tensor (input.h:96-115): (p - avg)/256, planar.  grid: (chunks, N)
+__global__ void __launch_bounds__(256) to_tensor_kernel(const uint8_t* __restrict__ img, float* __restrict__ x, const long long hw,
+                                                        const float ar, const float ag, const float ab_)
+{
+    const int n = blockIdx.y;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= hw) return;
+    const uint8_t* p = img + ((long long)n * hw + i) * 3;
+    float* o = x + (long long)n * 3 * hw + i;
+    o[0] = (float)(((double)((float)p[0] - ar)) / 256.0);
+    o[hw] = (float)(((double)((float)p[1] - ag)) / 256.0);
+    o[2 * hw] = (float)(((double)((float)p[2] - ab_)) / 256.0);
+}
+
+__global__ void __launch_bounds__(256) extract_tile_kernel(const uint8_t* __restrict__ img, const int IH, const int IW, const int left,
+                                                           const int top, float* __restrict__ x, const int TH, const int TW,
+                                                           const float ar, const float ag, const float ab_)
+{
+    const long long hw = (long long)TH * TW;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= hw) return;
+    const int ty = (int)(i / TW), tx = (int)(i % TW);
+    const int sy = min(max(top + ty, 0), IH - 1), sx = min(max(left + tx, 0), IW - 1);
+    const uint8_t* p = img + ((long long)sy * IW + sx) * 3;
+    x[i] = (float)(((double)((float)p[0] - ar)) / 256.0);
+    x[hw + i] = (float)(((double)((float)p[1] - ag)) / 256.0);
+    x[2 * hw + i] = (float)(((double)((float)p[2] - ab_)) / 256.0);
+}
+
+struct WLabel { uint16_t label; uint16_t pad; float weight; };
+
+// loss.h:3155-3190 with cpu::softmax (cpu_dlib.cpp:1326-1383); one thread per pixel, grid (chunks, N)
+__global__ void __launch_bounds__(256) loss_kernel(const float* __restrict__ logits, const WLabel* __restrict__ wl, float* __restrict__ grad,
+                                                   const int K, const long long hw, const double scale, double* __restrict__ loss_sum)
+{
+    __shared__ double red[8];
+    const int n = blockIdx.y;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double loss = 0.0;
+    if (i < hw) {
+        const float* s = logits + (long long)n * K * hw + i;
+        float* g = grad + (long long)n * K * hw + i;
+        float mx = -INFINITY;
+        for (int k = 0; k < K; ++k) mx = fmaxf(mx, __ldg(s + (long long)k * hw));
+        float sum = 0.f;
+        for (int k = 0; k < K; ++k) sum += expf(__ldg(s + (long long)k * hw) - mx);
+        const WLabel l = wl[(long long)n * hw + i];
+        const double ws = (double)l.weight * scale;
+        for (int k = 0; k < K; ++k) {
+            const float p = expf(__ldg(s + (long long)k * hw) - mx) / sum;
+            if (k == (int)l.label) {
+                loss += ws * (double)(-logf(fmaxf(p, 1e-10f)));
+                g[(long long)k * hw] = (float)(ws * (double)(p - 1.f));
+            } else
+                g[(long long)k * hw] = (float)(ws * (double)p);
+        }
+    }
+    loss = warp_sum(loss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = loss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        if (t != 0.0) atomicAdd(loss_sum, t);
+    }
+}
+
+__global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ planes, const long long plane_stride, const int K,
+                                                     const long long npix, const double* __restrict__ gains, uint16_t* __restrict__ labels)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    uint16_t label = 65535;
+    float best = -INFINITY;
+    for (int k = 0; k < K; ++k) {
+        const float raw = __ldg(planes + (long long)k * plane_stride + i);
+        const float v = gains ? (float)((double)raw + gains[k]) : raw;
+        if (v > best) { best = v; label = (uint16_t)k; }
+    }
+    labels[i] = label;
+}
+
+__device__ __forceinline__ double ramp(long long c, long long first_possible, long long first_in, long long last_in, long long last_possible)
+{
+    if (c < first_in) return (double)(c - first_possible) / (double)(first_in - first_possible);
+    if (c > last_in) return (double)(last_possible - c) / (double)(last_possible - last_in);
+    return 1.0;
+}
+
+// annonet_infer.cpp:116-164; one thread per tile pixel
+__global__ void __launch_bounds__(256) blend_kernel(const BlendArgs a)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)a.th * a.tw) return;
+    const int y = (int)(i / a.tw), x = (int)(i % a.tw);
+    const int by = a.top + y, bx = a.left + x;
+    if (by < a.full[1] || by > a.full[3] || bx < a.full[0] || bx > a.full[2]) return;
+    if (by < 0 || by >= a.H || bx < 0 || bx >= a.W) return;
+    const bool unique = bx >= a.unique[0] && bx <= a.unique[2] && by >= a.unique[1] && by <= a.unique[3];
+    const long long hw = (long long)a.H * a.W, thw = (long long)a.th * a.tw;
+    float* o = a.canvas + (long long)by * a.W + bx;
+    const float* s = a.logits + i;
+    if (unique) {
+        for (int k = 0; k < a.K; ++k) o[k * hw] = __ldg(s + k * thw);
+    } else {
+        const double t = ramp(bx, a.full[0], a.unique[0], a.unique[2], a.full[2]) * ramp(by, a.full[1], a.unique[1], a.unique[3], a.full[3]);
+        for (int k = 0; k < a.K; ++k) o[k * hw] = (float)((double)o[k * hw] + t * (double)__ldg(s + k * thw));
+    }
+}
+
+__global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ v,
+                                                  const float* __restrict__ lr_mul, const float* __restrict__ wd_mul, const long long n,
+                                                  const float lr, const float wd, const float momentum, const float grad_scale)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double lrm = (double)lr * (double)lr_mul[i];
+    const float B = (float)(-((double)wd * (double)wd_mul[i]) * lrm);
+    const float C = (float)(-lrm);
+    const float gi = grad_scale == 1.f ? g[i] : g[i] * grad_scale;
+    // tt::affine_transform(v, v, params, params_grad, momentum, B, C), solvers.h:177-184
+    const float nv = __fadd_rn(__fadd_rn(__fmul_rn(momentum, v[i]), __fmul_rn(B, w[i])), __fmul_rn(C, gi));
+    v[i] = nv;
+    w[i] = w[i] + nv;
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
+                                                   float* __restrict__ v, const float* __restrict__ lr_mul, const float* __restrict__ wd_mul,
+                                                   const long long n, const float alpha_base, const float lr, const float wd,
+                                                   const float b1, const float b2, const float grad_scale)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float lri = (float)((double)lr * (double)lr_mul[i]);
+    const float wdi = (float)((double)wd * (double)wd_mul[i]);
+    const float alpha = lri * alpha_base;
+    const float gg = wdi * w[i] + g[i] * grad_scale;
+    const float mi = b1 * m[i] + (1 - b1) * gg;
+    const float vi = b2 * v[i] + (1 - b2) * gg * gg;
+    m[i] = mi;
+    v[i] = vi;
+    w[i] += -alpha * mi / (sqrtf(vi) + 1e-8f);
+}
+
+}  // namespace
+
+void to_tensor(const uint8_t* img, float* x, int N, int H, int W, float ar, float ag, float ab_, cudaStream_t st)
+{
+    const long long hw = (long long)H * W;
+    to_tensor_kernel<<<dim3((unsigned)((hw + 255) / 256), N), 256, 0, st>>>(img, x, hw, ar, ag, ab_);
+    count_launch();
+}
+
+void extract_tile(const uint8_t* img, int IH, int IW, int left, int top, float* x, int TH, int TW, float ar, float ag, float ab_,
+                  cudaStream_t st)
+{
+    const long long hw = (long long)TH * TW;
+    extract_tile_kernel<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(img, IH, IW, left, top, x, TH, TW, ar, ag, ab_);
+    count_launch();
+}
+
+void loss_forward_backward(const float* logits, const void* wlabels, float* grad, int N, int K, int H, int W, double* loss_sum,
+                           cudaStream_t st)
+{
+    const long long hw = (long long)H * W;
+    cudaMemsetAsync(loss_sum, 0, sizeof(double), st);
+    const double scale = 1.0 / ((double)N * (double)H * (double)W);
+    loss_kernel<<<dim3((unsigned)((hw + 255) / 256), N), 256, 0, st>>>(logits, (const WLabel*)wlabels, grad, K, hw, scale, loss_sum);
+    count_launch();
+}
+
+void argmax_labels(const float* planes, long long plane_stride, int K, long long npix, const double* gains_dev, uint16_t* labels,
+                   cudaStream_t st)
+{
+    argmax_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(planes, plane_stride, K, npix, gains_dev, labels);
+    count_launch();
+}
+
+void blend_tile(const BlendArgs& a, cudaStream_t st)
+{
+    const long long n = (long long)a.th * a.tw;
+    blend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
+    count_launch();
+}
+
+void sgd_step(float* w, const float* g, float* v, const float* lr_mul, const float* wd_mul, long long n, float lr, float wd,
+              float momentum, float grad_scale, cudaStream_t st)
+{
+    sgd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, v, lr_mul, wd_mul, n, lr, wd, momentum, grad_scale);
+    count_launch();
+}
+
+void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul, const float* wd_mul, long long n, float t, float lr,
+               float wd, float beta1, float beta2, float grad_scale, cudaStream_t st)
+{
+    const float alpha_base = std::sqrt(1 - std::pow(beta2, t)) / (1 - std::pow(beta1, t));
+    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, m, v, lr_mul, wd_mul, n, alpha_base, lr, wd, beta1, beta2, grad_scale);
+    count_launch();
+}
+
+void fill_zero(void* p, size_t bytes, cudaStream_t st) { cudaMemsetAsync(p, 0, bytes, st); }
+
+}  // namespace k
+}  // namespace ab

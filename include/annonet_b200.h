@@ -98,6 +98,11 @@ ab_status ab_net_load_dlib(ab_net* net, const void* bytes, size_t n);
  * statistics folded in (layers.h:2144-2163).  *bytes is released with ab_free. */
 ab_status ab_net_save_dlib(ab_net* net, int as_runtime, void** bytes, size_t* n);
 
+/* Host-only codec check (no device needed): deserialize a dlib net stream and serialize it again,
+ * optionally converting net_type -> anet_type like RuntimeNet::operator=(TrainingNet).  A clean()ed
+ * reference stream transcodes to itself byte for byte. */
+ab_status ab_dlib_transcode(const void* bytes, size_t n, int as_runtime, void** out_bytes, size_t* out_n);
+
 /* ---- sizes: NetPimpl.cpp:137-146,246-285 --------------------------------------------------- */
 int ab_required_input_dimension(void);
 ab_status ab_recommended_input_dimension(int minimum, int* out);

@@ -140,20 +140,63 @@ def bn_inference(x, gamma, beta, rm, rv, eps):
     return (gamma.reshape(sh) * (x - rm.reshape(sh)) * invstd.reshape(sh) + beta.reshape(sh)).astype(F32)
 
 
+# How the per-channel batch-norm reductions are accumulated:
+#   "dlib_fp32": sequentially in fp32 in dlib's loop order (sample, channel, pixel) -- the faithful
+#                restatement of cpu_dlib.cpp:1127-1140,1228-1270.  This is what pins the oracle to the
+#                compiled reference (gradients agree to ~4e-5; tests/test_oracle_golden.py).
+#   "fp64":      exact sums.  dlib's fp32 running sums carry rounding noise that the ~40 stacked
+#                bn_ layers amplify to ~1e-2 on the deepest gradients of the narrow golden net; the CUDA
+#                engine accumulates in fp64, so it is compared with this mode at 1e-4 and with the
+#                reference's own vectors at the reference's noise floor (DESIGN.md "Parity").
+SUM_MODE = "dlib_fp32"
+
+
+def _channel_sum(a: np.ndarray) -> np.ndarray:
+    """sum over (n, y, x) per channel of an NCHW array, accumulated according to SUM_MODE."""
+    if SUM_MODE == "fp64":
+        return a.sum(axis=(0, 2, 3), dtype=np.float64)
+    c = a.shape[1]
+    flat = np.ascontiguousarray(a.transpose(1, 0, 2, 3)).reshape(c, -1).astype(F32)
+    return np.cumsum(flat, axis=1, dtype=F32)[:, -1]
+
+
 def bn_train(x, gamma, beta, eps):
     """batch_normalize_conv, cpu_dlib.cpp:1073-1182 (biased variance for normalisation)."""
     m = x.shape[0] * x.shape[2] * x.shape[3]
-    mean = (x.sum(axis=(0, 2, 3), dtype=np.float64) / m).astype(F32)
-    sq = (np.square(x, dtype=np.float64).sum(axis=(0, 2, 3)) / m).astype(F32)
+    if SUM_MODE == "fp64":
+        mean = (_channel_sum(x) / m).astype(F32)
+        sq = (_channel_sum(np.square(x, dtype=np.float64)) / m).astype(F32)
+    else:
+        mean = (_channel_sum(x) / F32(m)).astype(F32)
+        sq = (_channel_sum(x * x) / F32(m)).astype(F32)
     var = (sq - mean * mean).astype(F32)
-    invstd = (F32(1) / np.sqrt(var + F32(eps))).astype(F32)
+    invstd = (1.0 / np.sqrt(var.astype(np.float64) + eps)).astype(F32)
     sh = (1, -1, 1, 1)
     y = ((x - mean.reshape(sh)) * invstd.reshape(sh)) * gamma.reshape(sh) + beta.reshape(sh)
     return y.astype(F32), mean, invstd, var
 
 
+def _bn_backward_fp32(gy, x, gamma, mean, invstd):
+    """cpu_dlib.cpp:1228-1288 statement by statement, in fp32 with sequential sums."""
+    sh = (1, -1, 1, 1)
+    m = x.shape[0] * x.shape[2] * x.shape[3]
+    xc = (x - mean.reshape(sh)).astype(F32)
+    xhat = (xc * invstd.reshape(sh)).astype(F32)
+    dbeta = _channel_sum(gy)
+    dgamma = _channel_sum(gy * xhat)
+    dx = (gy * gamma.reshape(sh)).astype(F32)
+    invstd_pow = (F32(-0.5) * invstd ** 3).astype(F32)
+    dvars = _channel_sum(dx * xc * invstd_pow.reshape(sh))
+    invnum = F32(1.0 / m)
+    dmeans = _channel_sum((-dx * invstd.reshape(sh) + dvars.reshape(sh) * F32(-2) * xc * invnum).astype(F32))
+    out = dx * invstd.reshape(sh) + dvars.reshape(sh) * 2 * xc * invnum + dmeans.reshape(sh) * invnum
+    return out.astype(F32), dgamma.astype(F32), dbeta.astype(F32)
+
+
 def bn_backward(gy, x, gamma, mean, invstd):
     """batch_normalize_conv_gradient, cpu_dlib.cpp:1184-1289; returns (dx, dgamma, dbeta)."""
+    if SUM_MODE != "fp64":
+        return _bn_backward_fp32(gy, x, gamma, mean, invstd)
     sh = (1, -1, 1, 1)
     m = x.shape[0] * x.shape[2] * x.shape[3]
     gy64 = gy.astype(np.float64)
@@ -225,7 +268,7 @@ def forward(net: Net, x: np.ndarray, training: bool, update_running_stats: bool 
         if skip_dead and l.get("dead") and t == "con":
             ctx.out[i] = None
             continue
-        if xin is None:  # downstream of a skipped dead conv
+        if xin is None and t != "concat":  # downstream of a skipped dead conv (concat_ reads tags only)
             ctx.out[i] = None
             continue
         if t == "con":
