@@ -44,6 +44,10 @@ class _NetInfo(C.Structure):
                 ("num_params", C.c_int64), ("num_layers", C.c_int32), ("device", C.c_int32)]
 
 
+class _KernelStat(C.Structure):
+    _fields_ = [("name", C.c_char * 24), ("launches", C.c_uint64), ("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double)]
+
+
 class _Tile(C.Structure):
     _fields_ = [("full", C.c_int32 * 4), ("non_overlapping", C.c_int32 * 4), ("unique", C.c_int32 * 4)]
 
@@ -56,7 +60,7 @@ EXPORTS = [
     "ab_infer_tiled_partial", "ab_infer_finish", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
-    "ab_device_synchronize",
+    "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
 ]
 
 

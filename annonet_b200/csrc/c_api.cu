@@ -2,6 +2,7 @@
 #include "../../include/annonet_b200.h"
 
 #include "engine.h"
+#include "prof.h"
 #include "kcommon.cuh"
 #include "tiling.h"
 
@@ -301,6 +302,21 @@ ab_status ab_set_weights(const uint16_t* labels, int h, int w, double class_weig
     return guarded([&] {
         if (!labels || !weights_out || h <= 0 || w <= 0) throw std::invalid_argument("bad arguments");
         ab::set_weights(labels, h, w, class_weight, image_weight, weights_out);
+    });
+}
+
+ab_status ab_profile_enable(int on) { return guarded([&] { ab::k::prof_enable(on != 0); }); }
+ab_status ab_profile_read(ab_kernel_stat* out, int cap, int* count)
+{
+    return guarded([&] {
+        ab::k::FamilyStat st[ab::k::F_COUNT];
+        ab::k::prof_collect(st);
+        if (count) *count = ab::k::F_COUNT;
+        for (int i = 0; i < ab::k::F_COUNT && i < cap && out; ++i) {
+            std::memset(&out[i], 0, sizeof(out[i]));
+            std::strncpy(out[i].name, st[i].name, sizeof(out[i].name) - 1);
+            out[i].launches = st[i].launches; out[i].ms = st[i].ms; out[i].flops = st[i].flops; out[i].bytes = st[i].bytes;
+        }
     });
 }
 

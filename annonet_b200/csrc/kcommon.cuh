@@ -1,6 +1,7 @@
 // Shared device helpers of the fp32 kernels.
 #pragma once
 #include "kernels.h"
+#include "prof.h"
 
 #include <atomic>
 

@@ -208,6 +208,7 @@ inline dim3 ew_grid(long long hw, int C, int N) { return dim3((unsigned)((hw + E
 
 void bn_stats(const Slice& z, int N, int H, int W, int mish_first, double* sums, cudaStream_t st)
 {
+    ProfScope ps(F_BN, 3.0 * N * H * W * z.C, 4.0 * N * H * W * z.C, st);
     cudaMemsetAsync(sums, 0, sizeof(double) * 2 * z.C, st);
     const long long hw = (long long)H * W;
     bn_stats_kernel<<<ew_grid(hw, z.C, N), EW_T, 0, st>>>(z, hw, mish_first, sums);
@@ -224,6 +225,7 @@ void bn_finalize(const double* sums, int C, long long m, float eps, double decay
 void bn_apply(const Slice& z, const Slice& y, int N, int H, int W, int mish_first, int has_mish, const float* gamma,
               const float* beta, const float* stats, cudaStream_t st)
 {
+    ProfScope ps(F_BN, 4.0 * N * H * W * z.C, 8.0 * N * H * W * z.C, st);
     const long long hw = (long long)H * W;
     bn_apply_kernel<<<ew_grid(hw, z.C, N), EW_T, 0, st>>>(z, y, hw, mish_first, has_mish, gamma, beta, stats);
     count_launch();
@@ -232,6 +234,7 @@ void bn_apply(const Slice& z, const Slice& y, int N, int H, int W, int mish_firs
 void bn_backward_reduce(const Slice& z, const Slice& gy, int N, int H, int W, int mish_first, int has_mish, const float* gamma,
                         const float* beta, const float* stats, double* red, cudaStream_t st)
 {
+    ProfScope ps(F_BN, 6.0 * N * H * W * z.C, 8.0 * N * H * W * z.C, st);
     cudaMemsetAsync(red, 0, sizeof(double) * 2 * z.C, st);
     const long long hw = (long long)H * W;
     bn_bwd_reduce_kernel<<<ew_grid(hw, z.C, N), EW_T, 0, st>>>(z, gy, hw, mish_first, has_mish, gamma, beta, stats, red);
@@ -242,6 +245,7 @@ void bn_backward_apply(const Slice& z, const Slice& gy, float* dz, int N, int H,
                        const float* gamma, const float* beta, const float* stats, const double* red, float* dgamma,
                        float* dbeta, cudaStream_t st)
 {
+    ProfScope ps(F_BN, 8.0 * N * H * W * z.C, 12.0 * N * H * W * z.C, st);
     const long long hw = (long long)H * W;
     const float invnum = 1.0f / (float)((long long)N * hw);
     bn_bwd_apply_kernel<<<ew_grid(hw, z.C, N), EW_T, 0, st>>>(z, gy, dz, hw, mish_first, has_mish, gamma, beta, stats, red, invnum,
@@ -251,6 +255,7 @@ void bn_backward_apply(const Slice& z, const Slice& gy, float* dz, int N, int H,
 
 void maxpool_forward(const Slice& in, const Slice& out, int N, int Hin, int Win, cudaStream_t st)
 {
+    ProfScope ps(F_POOL, 0, 4.0 * N * in.C * ((double)Hin * Win + (double)(1 + (Hin - 3) / 2) * (1 + (Win - 3) / 2)), st);
     const int Ho = 1 + (Hin - 3) / 2, Wo = 1 + (Win - 3) / 2;
     maxpool_fwd_kernel<<<dim3((unsigned)(((long long)Ho * Wo + 255) / 256), in.C, N), 256, 0, st>>>(in, out, Hin, Win, Ho, Wo);
     count_launch();
@@ -258,6 +263,7 @@ void maxpool_forward(const Slice& in, const Slice& out, int N, int Hin, int Win,
 
 void maxpool_backward(const Slice& in, const Slice& gout, const Slice& gin, int N, int Hin, int Win, cudaStream_t st)
 {
+    ProfScope ps(F_POOL, 0, 4.0 * N * in.C * (3.0 * Hin * Win + (double)(1 + (Hin - 3) / 2) * (1 + (Win - 3) / 2)), st);
     const int Ho = 1 + (Hin - 3) / 2, Wo = 1 + (Win - 3) / 2;
     maxpool_bwd_kernel<<<dim3((unsigned)(((long long)Hin * Win + 255) / 256), in.C, N), 256, 0, st>>>(in, gout, gin, Hin, Win, Ho, Wo);
     count_launch();

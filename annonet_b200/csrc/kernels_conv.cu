@@ -198,6 +198,8 @@ void launch1x1(const ConvArgs& a, cudaStream_t st)
 
 void conv3x3(const ConvArgs& a, cudaStream_t st)
 {
+    const double px = (double)a.N * a.H * a.W;
+    ProfScope ps(F_CONV3X3, 18.0 * px * a.in.C * a.out.C, 4.0 * px * (a.in.C + a.out.C * (a.accumulate ? 2 : 1)), st);
     switch (pick_co_tile(a.out.C)) {
     case 8: launch3x3<8>(a, st); break;
     case 24: launch3x3<24>(a, st); break;
@@ -207,6 +209,8 @@ void conv3x3(const ConvArgs& a, cudaStream_t st)
 
 void conv1x1(const ConvArgs& a, cudaStream_t st)
 {
+    const double px = (double)a.N * a.H * a.W, pin = a.pool ? (double)a.N * a.Hin * a.Win : px;
+    ProfScope ps(F_CONV1X1, 2.0 * px * a.in.C * a.out.C, 4.0 * (pin * a.in.C + px * a.out.C * (a.accumulate ? 2 : 1)), st);
     if (a.out.C <= 8 || (a.out.C % 16 != 0 && a.out.C % 8 == 0)) launch1x1<8>(a, st);
     else launch1x1<16>(a, st);
 }

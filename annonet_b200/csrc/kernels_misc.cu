@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ w, const 
 
 void to_tensor(const uint8_t* img, float* x, int N, int H, int W, float ar, float ag, float ab_, cudaStream_t st)
 {
+    ProfScope ps(F_INPUT, 0, 15.0 * N * H * W, st);
     const long long hw = (long long)H * W;
     to_tensor_kernel<<<dim3((unsigned)((hw + 255) / 256), N), 256, 0, st>>>(img, x, hw, ar, ag, ab_);
     count_launch();
@@ -161,6 +162,7 @@ void to_tensor(const uint8_t* img, float* x, int N, int H, int W, float ar, floa
 void extract_tile(const uint8_t* img, int IH, int IW, int left, int top, float* x, int TH, int TW, float ar, float ag, float ab_,
                   cudaStream_t st)
 {
+    ProfScope ps(F_INPUT, 0, 15.0 * TH * TW, st);
     const long long hw = (long long)TH * TW;
     extract_tile_kernel<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(img, IH, IW, left, top, x, TH, TW, ar, ag, ab_);
     count_launch();
@@ -169,6 +171,7 @@ void extract_tile(const uint8_t* img, int IH, int IW, int left, int top, float* 
 void loss_forward_backward(const float* logits, const void* wlabels, float* grad, int N, int K, int H, int W, double* loss_sum,
                            cudaStream_t st)
 {
+    ProfScope ps(F_LOSS, 0, (8.0 * K + 8.0) * N * H * W, st);
     const long long hw = (long long)H * W;
     cudaMemsetAsync(loss_sum, 0, sizeof(double), st);
     const double scale = 1.0 / ((double)N * (double)H * (double)W);
@@ -179,12 +182,14 @@ void loss_forward_backward(const float* logits, const void* wlabels, float* grad
 void argmax_labels(const float* planes, long long plane_stride, int K, long long npix, const double* gains_dev, uint16_t* labels,
                    cudaStream_t st)
 {
+    ProfScope ps(F_ARGMAX, 0, (4.0 * K + 2.0) * npix, st);
     argmax_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(planes, plane_stride, K, npix, gains_dev, labels);
     count_launch();
 }
 
 void blend_tile(const BlendArgs& a, cudaStream_t st)
 {
+    ProfScope ps(F_BLEND, 0, 12.0 * a.K * a.th * a.tw, st);
     const long long n = (long long)a.th * a.tw;
     blend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
     count_launch();
@@ -193,6 +198,7 @@ void blend_tile(const BlendArgs& a, cudaStream_t st)
 void sgd_step(float* w, const float* g, float* v, const float* lr_mul, const float* wd_mul, long long n, float lr, float wd,
               float momentum, float grad_scale, cudaStream_t st)
 {
+    ProfScope ps(F_OPTIMIZER, 0, 28.0 * n, st);
     sgd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, v, lr_mul, wd_mul, n, lr, wd, momentum, grad_scale);
     count_launch();
 }
@@ -200,6 +206,7 @@ void sgd_step(float* w, const float* g, float* v, const float* lr_mul, const flo
 void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul, const float* wd_mul, long long n, float t, float lr,
                float wd, float beta1, float beta2, float grad_scale, cudaStream_t st)
 {
+    ProfScope ps(F_OPTIMIZER, 0, 36.0 * n, st);
     const float alpha_base = std::sqrt(1 - std::pow(beta2, t)) / (1 - std::pow(beta1, t));
     adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, m, v, lr_mul, wd_mul, n, alpha_base, lr, wd, beta1, beta2, grad_scale);
     count_launch();

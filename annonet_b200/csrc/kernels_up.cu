@@ -130,6 +130,7 @@ __global__ void __launch_bounds__(128) up_backward_data_kernel(const Slice gout,
 
 void up_forward(const Slice& in, const Slice& out, int N, int h, int w, const float* wt, const float* bias, cudaStream_t st)
 {
+    ProfScope ps(F_UP, 18.0 * N * h * w * in.C * out.C, 4.0 * N * ((double)h * w * in.C + (2.0 * h + 1) * (2.0 * w + 1) * out.C), st);
     const int quads = (h + 1) * (w + 1);
     dim3 grid((quads + 127) / 128, (out.C + UP_CO_T - 1) / UP_CO_T, N);
     up_forward_kernel<<<grid, 128, 0, st>>>(in, out, h, w, wt, bias);
@@ -138,6 +139,7 @@ void up_forward(const Slice& in, const Slice& out, int N, int h, int w, const fl
 
 void up_backward_data(const Slice& gout, const Slice& gin, int N, int h, int w, const float* wt, cudaStream_t st)
 {
+    ProfScope ps(F_UP, 18.0 * N * h * w * gin.C * gout.C, 4.0 * N * (2.0 * h * w * gin.C + (2.0 * h + 1) * (2.0 * w + 1) * gout.C), st);
     dim3 grid((unsigned)(((long long)h * w + 127) / 128), (gin.C + 15) / 16, N);
     up_backward_data_kernel<<<grid, 128, 0, st>>>(gout, gin, h, w, wt);
     count_launch();

@@ -167,6 +167,7 @@ size_t wgrad_scratch_floats(int, int) { return kScratchFloats; }
 void wgrad3x3(const Slice& A, const Slice& B, int N, int Ha, int Wa, int Hb, int Wb, int S, int P, float* g, float* scratch,
               cudaStream_t st)
 {
+    ProfScope ps(F_WGRAD, 18.0 * N * Ha * Wa * A.C * B.C, 4.0 * N * ((double)Ha * Wa * A.C + (double)Hb * Wb * B.C), st);
     const int TH = S == 1 ? 8 : 4;
     const int tiles_x = (Wa + 31) / 32, tiles_y = (Ha + TH - 1) / TH;
     const int chunks = ((B.C + WG_B - 1) / WG_B) * ((A.C + WG_A - 1) / WG_A);
@@ -182,6 +183,7 @@ void wgrad3x3(const Slice& A, const Slice& B, int N, int Ha, int Wa, int Hb, int
 
 void wgrad1x1(const Slice& A, const Slice& B, int N, int H, int W, float* g, float* scratch, cudaStream_t st)
 {
+    ProfScope ps(F_WGRAD, 2.0 * N * H * W * A.C * B.C, 4.0 * N * H * W * (A.C + B.C), st);
     const long long hw = (long long)H * W;
     const int cps = (int)((hw + 255) / 256);
     const int chunks = ((B.C + WG_B - 1) / WG_B) * ((A.C + WG_A - 1) / WG_A);
@@ -195,6 +197,7 @@ void wgrad1x1(const Slice& A, const Slice& B, int N, int H, int W, float* g, flo
 
 void channel_sum(const Slice& A, int N, int H, int W, float* g, float* scratch, cudaStream_t st)
 {
+    ProfScope ps(F_BIAS_GRAD, 1.0 * N * H * W * A.C, 4.0 * N * H * W * A.C, st);
     const long long hw = (long long)H * W;
     long long s = ((long long)N * hw + 256 * 16 - 1) / (256 * 16);
     const int splits = (int)(s < 1 ? 1 : (s > 64 ? 64 : s));

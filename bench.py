@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of annonet on B200, measured.
+
+Headline (BASELINE.json configs[1]): one annonet_train step -- 32 crops of 255 x 255 (the 64w+63 size the
+CLI feeds for "256"), 3 classes, weighted per-pixel loss, SGD -- in crops/s.  A "step" is one
+forward + loss + backward + update over one synthetic minibatch.
+
+  python bench.py --gpus N --steps K --warmup W            our engine (libannonet_b200.so through the C ABI)
+  python bench.py --impl reference ...                      the reference's own dlib CPU build (oracle/_ref/annonet_ref)
+
+`value`  : device-resident inputs, CUDA events on the engine's stream, max over ranks.
+`e2e`    : the same steps through ab_train_step_async with HOST buffers (H2D of crops + labels every step,
+           8-byte loss read back every step), timed on the host between device synchronizes.
+`roofline`: the family of kernels with the largest share of the step, timed live with CUDA event pairs
+           (ab_profile_*) during the timed region; algorithmic flops/bytes as DESIGN.md defines them.
+Also reported (not the headline): tiled inference of one 1024 x 1024 image (configs[0]) in Mpix/s.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CROP, BATCH, CLASSES = 255, 32, 3
+INFER_SIZE, INFER_TILE = 1024, 1024
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "annonet_ref")
+FWD_FLOP_PER_PX = 170281.0  # live layers, SURVEY §8d
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        p.update({k: m[k] for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained") if k in m})
+        p["source"] = "measured"
+    except Exception:
+        pass
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.12)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def synthetic_batch(n, h, w, k, seed):
+    """seeded u8 crops (smooth sinusoids + noise so the batch-norm statistics are not degenerate), blocky
+    labels with 5 % ignored pixels, weights from set_weights(0.5, 0.5) like annonet_train_main.cpp:214-232."""
+    import numpy as np
+    import annonet_b200 as ab
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    imgs = np.empty((n, h, w, 3), np.uint8)
+    labels = np.empty((n, h, w), np.uint16)
+    weights = np.empty((n, h, w), np.float32)
+    for i in range(n):
+        img = np.zeros((h, w, 3), np.float32)
+        for c in range(3):
+            for _ in range(3):
+                fx, fy, ph = rng.uniform(0.01, 0.08), rng.uniform(0.01, 0.08), rng.uniform(0, 6.28)
+                img[:, :, c] += rng.uniform(20, 50) * np.sin(fx * xx + fy * yy + ph)
+        img += 128 + rng.normal(0, 12, size=img.shape)
+        imgs[i] = np.clip(img, 0, 255).astype(np.uint8)
+        lab = ((((yy.astype(np.int64) + 7 * i) // 16) + (xx.astype(np.int64) // 16)) % k).astype(np.uint16)
+        lab[rng.random((h, w)) < 0.05] = 65535
+        labels[i] = lab
+        weights[i] = ab.set_weights(lab, 0.5, 0.5)
+    return imgs, ab.pack_labels(labels, weights)
+
+
+# ---- the reference's own CPU implementation (oracle/_ref/annonet_ref: unmodified dlib CPU build) --------------
+def _ref(*args, timeout=3000):
+    env = dict(os.environ)
+    env.setdefault("OMP_NUM_THREADS", str(os.cpu_count() or 1))
+    r = subprocess.run([REF_BIN, *map(str, args)], check=True, capture_output=True, text=True, timeout=timeout, env=env)
+    return r.stdout
+
+
+def reference_train(sample_crops, steps):
+    """StartTraining x steps + sync of the reference (NetPimpl::TrainingNet, dlib CPU backend) on
+    `sample_crops` crops of CROP x CROP: a bounded sample of the 32-crop minibatch (per-crop cost is
+    independent of the minibatch size on the CPU path: per-sample im2col + sgemm, cpu_dlib.cpp:2250-2355)."""
+    with tempfile.TemporaryDirectory() as tmp:
+        cfg, net = os.path.join(tmp, "cfg.net"), os.path.join(tmp, "net.dnn")
+        _ref("config", CLASSES, 1.0, 1, cfg)
+        _ref("materialize", cfg, net, 5)
+        out = json.loads(_ref("bench_train", net, sample_crops, CROP, CROP, steps).strip().splitlines()[-1])
+    return out
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    if not os.access(REF_BIN, os.X_OK):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/annonet_ref was not built (needs /root/reference at build time)"}))
+        return 0
+    sample, steps = 2, max(1, min(args.steps, 3))
+    out = reference_train(sample, steps)
+    v = float(out["crops_per_s"])
+    line = {
+        "impl": "reference", "metric": "train_crops_per_s", "value": v, "unit": "crops/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": 0, "ms_per_step": 1e3 * float(out["seconds"]) / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP}, {CLASSES} classes, weighted per-pixel loss, SGD (BASELINE configs[1])",
+                   "net": "net_type LEVEL_COUNT=6 full width, 2,279,571 params, random init"},
+        "cpu_baseline": {"value": v, "unit": "crops/s", "cores": int(out.get("threads", 1)), "kind": "reference",
+                         "sample": f"{steps} step(s) of {sample} crops {CROP}x{CROP} (of the {BATCH}-crop minibatch); dlib CPU build, no BLAS, OpenMP im2col"},
+        "e2e": {"value": v, "unit": "crops/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---- our engine -----------------------------------------------------------------------------------------------
+def own_arm(args):
+    import ctypes as C
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import annonet_b200 as ab
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    precision = ab.AB_PRECISION_BF16 if args.precision == "bf16" else ab.AB_PRECISION_FP32
+
+    net = ab.TrainingNet(local, precision)
+    net.Initialize(CLASSES, 1.0, 1, seed=1)         # identical weights on every rank (same seed)
+    net.SetLearningRate(1e-3)
+    if world > 1:                                    # engine-owned NCCL communicator; id travels through torch.distributed
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(ab.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        net.comm_init(bytes(uid.cpu().numpy().tobytes()), rank, world)
+
+    imgs, wl = synthetic_batch(BATCH, CROP, CROP, CLASSES, seed=1234 + rank)
+    h_imgs = torch.from_numpy(imgs).pin_memory()
+    h_wl = torch.from_numpy(wl.view(np.uint8).reshape(BATCH, CROP, CROP, 8)).pin_memory()
+    d_imgs, d_wl = h_imgs.cuda(), h_wl.cuda()
+    stream = torch.cuda.ExternalStream(net.stream(), device=local)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        net.train_step_device(d_imgs.data_ptr(), d_wl.data_ptr(), BATCH, CROP, CROP)
+
+    def step_host():
+        ab._check(ab.lib.ab_train_step_async(net.handle, C.c_void_p(h_imgs.data_ptr()), C.c_void_p(h_wl.data_ptr()), BATCH, CROP, CROP))
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    loss0 = net.sync()
+
+    # ---- value: K steps, inputs resident in HBM; working set per step (~5 GB of activations) >> 126 MB L2
+    launches0 = net.kernel_launches()
+    ab._check(ab.lib.ab_profile_enable(1))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with ClockSampler(local) as clocks:
+        e0.record(stream)
+        for _ in range(args.steps):
+            step_device()
+        e1.record(stream)
+        loss = net.sync()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = net.kernel_launches() - launches0
+    stats = (ab._KernelStat * 32)()
+    cnt = C.c_int(0)
+    ab._check(ab.lib.ab_profile_read(stats, 32, C.byref(cnt)))
+    ab._check(ab.lib.ab_profile_enable(0))
+    fam = [{"name": s.name.decode(), "launches": int(s.launches), "ms": s.ms, "flops": s.flops, "bytes": s.bytes}
+           for s in stats[:cnt.value] if s.launches]
+
+    # ---- e2e: host buffers through the C ABI
+    for _ in range(2):
+        step_host()
+    net.sync()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    net.sync()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+
+    # ---- secondary: tiled inference of a 1024 x 1024 image (configs[0]); rank 0 only
+    infer = None
+    if rank == 0 and not args.no_infer:
+        infer = bench_infer(ab, net, local, precision, torch)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    pk = peaks()
+    total_ms = sum(f["ms"] for f in fam) or 1.0
+    top = max(fam, key=lambda f: f["ms"])
+    tensor_bound = top["name"] in ("conv3x3", "conv1x1", "up_cont", "wgrad")
+    avg_ms = top["ms"] / top["launches"]
+    if tensor_bound:
+        achieved = top["flops"] / (top["ms"] * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": achieved / pk["bf16_tflops_sustained"]}
+    else:
+        achieved = top["bytes"] / (top["ms"] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"]}
+    roof.update({"traffic": None, "kernel": top["name"], "avg_launch_ms": avg_ms, "share_of_step": top["ms"] / total_ms,
+                 "peak_source": pk["source"] + (" (sustained bf16 cuBLAS)" if tensor_bound else " (copy)")})
+    families = {f["name"]: {"launches_per_step": f["launches"] / args.steps, "ms_per_step": f["ms"] / args.steps,
+                            "tflops": f["flops"] / (f["ms"] * 1e-3) / 1e12 if f["flops"] else None,
+                            "gbs": f["bytes"] / (f["ms"] * 1e-3) / 1e9} for f in sorted(fam, key=lambda f: -f["ms"])}
+
+    cpu = None
+    if world == 1 and not args.no_cpu and os.access(REF_BIN, os.X_OK):
+        out = reference_train(2, 1)
+        cpu = {"value": float(out["crops_per_s"]), "unit": "crops/s", "cores": int(out.get("threads", 1)), "kind": "reference",
+               "sample": f"1 step of 2 crops {CROP}x{CROP} (of the {BATCH}-crop minibatch) by oracle/_ref/annonet_ref: dlib CPU build, no BLAS, OpenMP im2col"}
+
+    crops = BATCH * world * args.steps
+    line = {
+        "metric": "train_crops_per_s", "value": crops / (ms * 1e-3), "unit": "crops/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if precision == ab.AB_PRECISION_FP32 else "bf16 (fp32 accumulate)", "data": "synthetic",
+        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP} per GPU, {CLASSES} classes, weighted per-pixel loss, SGD (BASELINE configs[1])",
+                   "net": "net_type LEVEL_COUNT=6 full width, 2,279,571 params, random init", "parallelism": f"dp{world}",
+                   "l2": "no flush: each step streams ~5 GB of activations, far beyond the 126 MB L2",
+                   "train_tflops_algorithmic": 3 * FWD_FLOP_PER_PX * CROP * CROP * crops / (ms * 1e-3) / 1e12},
+        "clocks": clocks.summary(),
+        "e2e": {"value": crops / (e2e_ms * 1e-3), "unit": "crops/s", "h2d_bytes_per_step": int(h_imgs.numel() + h_wl.numel()),
+                "d2h_bytes_per_step": 8, "timer": "host clock between device synchronizes, max over ranks"},
+        "gpu_launches": int(launches),
+        "roofline": roof, "kernel_families": families, "cpu_baseline": cpu,
+        "loss": {"after_warmup": loss0, "last": loss}, "inference": infer,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_infer(ab, train_net, device, precision, torch, reps=3):
+    """annonet_infer() equivalent on one 1024 x 1024 RGB image, 3 classes (BASELINE configs[0]): tiles ->
+    forward -> blend -> argmax.  device-resident (image + label map in HBM) and e2e (host image in, host labels out)."""
+    import numpy as np
+    rt = train_net.GetRuntimeNet(device, precision)
+    rng = np.random.default_rng(99)
+    img = rng.integers(0, 256, size=(INFER_SIZE, INFER_SIZE, 3), dtype=np.uint8)
+    d_img = torch.from_numpy(img).cuda()
+    d_lab = torch.empty((INFER_SIZE, INFER_SIZE), dtype=torch.int16, device="cuda")
+    stream = torch.cuda.ExternalStream(rt.stream(), device=device)
+    for _ in range(2):
+        rt.infer_device(d_img.data_ptr(), INFER_SIZE, INFER_SIZE, INFER_TILE, INFER_TILE, d_lab.data_ptr())
+    rt.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        rt.infer_device(d_img.data_ptr(), INFER_SIZE, INFER_SIZE, INFER_TILE, INFER_TILE, d_lab.data_ptr())
+    e1.record(stream)
+    rt.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        rt.infer(img, INFER_TILE, INFER_TILE)
+    e2e = (time.perf_counter() - t0) / reps
+    npix = INFER_SIZE * INFER_SIZE
+    tile = ab.recommended_input_dimension(INFER_SIZE)
+    return {"workload": f"annonet_infer of one {INFER_SIZE}x{INFER_SIZE} RGB image, {CLASSES} classes, tile {INFER_TILE} (1 tile run at {tile}x{tile})",
+            "mpix_per_s": npix / (ms * 1e-3) / 1e6, "ms": ms, "e2e_mpix_per_s": npix / e2e / 1e6,
+            "tflops_algorithmic": FWD_FLOP_PER_PX * tile * tile / (ms * 1e-3) / 1e12}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("AB_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-infer", action="store_true", help="skip the secondary inference measurement")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return own_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

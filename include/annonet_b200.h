@@ -171,6 +171,16 @@ ab_status ab_comm_init(ab_net* net, const void* id128, int rank, int world);
 ab_status ab_set_weights(const uint16_t* labels, int h, int w, double class_weight, double image_weight, float* weights_out);
 
 /* ---- instrumentation ---------------------------------------------------------------------- */
+/* Device time per kernel family, measured with CUDA event pairs on the engine's stream around every
+ * launch while enabled (bench.py's roofline figures).  flops/bytes are the ALGORITHMIC work of the
+ * bracketed launches (DESIGN.md "Algorithmic work").  Process-wide; ab_profile_enable(1) restarts. */
+typedef struct {
+    char name[24];
+    uint64_t launches;
+    double ms, flops, bytes;
+} ab_kernel_stat;
+ab_status ab_profile_enable(int on);
+ab_status ab_profile_read(ab_kernel_stat* out, int cap, int* count);
 void* ab_stream(ab_net* net);              /* cudaStream_t the engine launches on */
 uint64_t ab_kernel_launches(ab_net* net);   /* kernels of this library launched so far on this net */
 ab_status ab_device_synchronize(ab_net* net);
