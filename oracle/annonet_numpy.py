@@ -539,7 +539,7 @@ def _get_t(c, first_possible, first_in, last_in, last_possible):
 
 
 def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int, gains: Sequence[float] = (),
-                  overlap: Optional[int] = None, return_blended: bool = False):
+                  overlap: Optional[int] = None, return_blended: bool = False, forward_fn=None):
     """annonet_infer(), annonet_infer.cpp:32-185 (without the detection-level blob filter):
     tiles -> enlarge to the recommended size around the centre -> clamp-to-edge fill (outpaint,
     annonet.h:74-120) -> Forward -> blend (double ramps, float accumulate) -> argmax."""
@@ -558,8 +558,11 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
         ys = np.clip(np.arange(top, top + rh), 0, h - 1)
         xs = np.clip(np.arange(left, left + rw), 0, w - 1)
         chip = image[ys][:, xs]
-        x = to_tensor(chip[None], anet.layers[-1]["avg"])
-        out = logits_of(forward(anet, x, training=False, skip_dead=True))[0]
+        if forward_fn is not None:   # tests: check the scheduler / blend / argmax at sizes the numpy net cannot reach
+            out = forward_fn(np.ascontiguousarray(chip))
+        else:
+            x = to_tensor(chip[None], anet.layers[-1]["avg"])
+            out = logits_of(forward(anet, x, training=False, skip_dead=True))[0]
         k = out.shape[0]
         if blended is None:
             blended = np.zeros((k, h, w), dtype=F32)
