@@ -7,6 +7,7 @@
 #include "kernels.h"
 #include "net_model.h"
 #include "plan.h"
+#include "tc.h"
 
 #include <cuda_runtime.h>
 #include <memory>
@@ -46,6 +47,7 @@ struct Hyper {
 };
 
 struct NcclApi;
+struct TcState;  // bf16 tensor-core path: workspaces, packed filters, launch descriptors (engine_bf16.cu)
 
 class Engine {
 public:
@@ -101,6 +103,14 @@ private:
     void optimizer_step();
     void allreduce_range(size_t lo, size_t hi);
     k::Slice level_slice(Levels& L, int level, int c0, int C) const;
+    // bf16 tensor-core path (precision_ == AB_PRECISION_BF16)
+    void tc_ensure_infer(int h, int w);
+    void tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w);
+    void tc_run_inference(int h, int w);
+    void tc_pack_forward_filters();
+    void tc_ensure_train(int n, int h, int w);
+    void tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
+    std::unique_ptr<TcState> tc_;
 
     int device_, precision_;
     cudaStream_t stream_ = nullptr, comm_stream_ = nullptr;

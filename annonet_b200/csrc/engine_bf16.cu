@@ -1,0 +1,212 @@
+// bf16 tensor-core path of the engine (AB_PRECISION_BF16): the same conv groups as the fp32 path
+// (plan.h), executed as tcgen05 implicit GEMMs over padded flat NHWC bf16 tensors (tc.h).
+#include "engine.h"
+#include "tc_state.h"
+
+#include <cstring>
+
+namespace ab {
+
+using tc::bf16;
+using tc::ConvLaunch;
+using tc::ConvSetup;
+using tc::Geo;
+
+namespace {
+
+// taps of one launch of a group in the forward direction: (dy, dx) offsets on the M grid and the index of
+// the filter tap in the arena ([..][ky*3 + kx])
+void forward_taps(const ConvGroup& g, TcGroup& t)
+{
+    t.nlaunch = 1;
+    if (g.ksize == 1) {
+        t.fwd_ntaps[0] = 1;
+        t.fwd_tapmap[0][0] = 0; t.fwd_tapdy[0][0] = 0; t.fwd_tapdx[0][0] = 0;
+    } else if (!g.is_cont) {           // con_ 3x3 s1 p1: out[y][x] += w[ky][kx] * in[y+ky-1][x+kx-1]
+        t.fwd_ntaps[0] = 9;
+        for (int ky = 0; ky < 3; ++ky)
+            for (int kx = 0; kx < 3; ++kx) { const int i = ky * 3 + kx; t.fwd_tapmap[0][i] = i; t.fwd_tapdy[0][i] = ky - 1; t.fwd_tapdx[0][i] = kx - 1; }
+    } else if (g.stride == 1) {        // cont_ 3x3 s1 p1: out[Y][X] += w[ky][kx] * in[Y-ky+1][X-kx+1]   (layers.h:531)
+        t.fwd_ntaps[0] = 9;
+        for (int ky = 0; ky < 3; ++ky)
+            for (int kx = 0; kx < 3; ++kx) { const int i = ky * 3 + kx; t.fwd_tapmap[0][i] = i; t.fwd_tapdy[0][i] = 1 - ky; t.fwd_tapdx[0][i] = 1 - kx; }
+    } else {
+        // cont_ 3x3 s2 p0 ("up"): out[2r+a][2c+b] += w[ky][kx] * in[r + (a-ky)/2][c + (b-kx)/2] for ky = a (mod 2), kx = b (mod 2).
+        // M position (r, c) of the coarse grid sits one row and one column before pixel (r, c): pixel (i, j) is at
+        // offset (i - r + 1)*P + (j - c + 1).
+        t.nlaunch = 4;
+        for (int a = 0; a < 2; ++a)
+            for (int b = 0; b < 2; ++b) {
+                const int l = a * 2 + b;
+                int n = 0;
+                for (int ky = a; ky < 3; ky += 2)
+                    for (int kx = b; kx < 3; kx += 2) {
+                        t.fwd_tapmap[l][n] = ky * 3 + kx;
+                        t.fwd_tapdy[l][n] = (a - ky) / 2 + 1;
+                        t.fwd_tapdx[l][n] = (b - kx) / 2 + 1;
+                        ++n;
+                    }
+                t.fwd_ntaps[l] = n;
+            }
+    }
+}
+
+}  // namespace
+
+// (re)build the bf16 filter packs of the forward direction from the fp32 parameter arena
+void Engine::tc_pack_forward_filters()
+{
+    if (!tc_) tc_ = std::make_unique<TcState>();
+    TcState& T = *tc_;
+    if (T.groups.size() != plan_.groups.size()) {
+        T.groups.assign(plan_.groups.size(), TcGroup());
+        size_t off = 0;
+        for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+            const ConvGroup& g = plan_.groups[gi];
+            TcGroup& t = T.groups[gi];
+            forward_taps(g, t);
+            t.npad = tc::padded_n(g.cout);
+            const int cin = g.in_level < 0 ? 8 : g.cin;
+            for (int l = 0; l < t.nlaunch; ++l) {
+                t.fwd_pack_off[l] = off;
+                off += (tc::packed_filter_elems(cin, t.npad, t.fwd_ntaps[l]) + 511) / 512 * 512;  // keep 1 KB alignment
+            }
+        }
+        T.fwd_packs.reserve(off * sizeof(bf16));
+        T.fwd_packs_valid = false;
+    }
+    if (T.fwd_packs_valid) return;
+    const float* P = params_.as<float>();
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        const TcGroup& t = T.groups[gi];
+        const int kk = g.ksize * g.ksize;
+        // arena: con_ [cout][cin][kk], cont_ [cin][cout][kk]
+        const long long sn = g.is_cont ? kk : (long long)g.cin * kk, sk = g.is_cont ? (long long)g.cout * kk : kk;
+        for (int l = 0; l < t.nlaunch; ++l)
+            tc::pack_filters_bf16(P + g.w_off, T.fwd_packs.as<bf16>() + t.fwd_pack_off[l], g.cout, t.npad, g.cin, t.fwd_ntaps[l],
+                                  t.fwd_tapmap[l], sn, sk, stream_);
+    }
+    AB_CUDA(cudaGetLastError());
+    T.fwd_packs_valid = true;
+}
+
+namespace {
+
+// workspace of padded flat NHWC level buffers for n samples of h x w
+void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, cudaStream_t st)
+{
+    if (ws.n == n && ws.h == h && ws.w == w) return;
+    const LevelDims d = level_dims(h, w, plan.levels);
+    for (int l = 0; l <= plan.levels; ++l) {
+        ws.geo[l].N = n; ws.geo[l].H = d.h[l]; ws.geo[l].W = d.w[l];
+        const size_t bytes = (size_t)ws.geo[l].positions() * plan.level_channels[l] * sizeof(bf16);
+        ws.level[l].reserve(bytes);
+        AB_CUDA(cudaMemsetAsync(ws.level[l].p, 0, bytes, st));  // pad positions must be zero and stay zero
+    }
+    if (with_image) {
+        const size_t bytes = (size_t)ws.geo[0].positions() * 8 * sizeof(bf16);
+        ws.img.reserve(bytes);
+        AB_CUDA(cudaMemsetAsync(ws.img.p, 0, bytes, st));
+    }
+    if (with_pool) {
+        ws.pool_off.assign(plan.groups.size(), 0);
+        size_t off = 0;
+        for (size_t gi = 0; gi < plan.groups.size(); ++gi) {
+            const ConvGroup& g = plan.groups[gi];
+            if (!g.pool_input) continue;
+            ws.pool_off[gi] = off;
+            off += ((size_t)ws.geo[g.out_level].positions() * g.cin + 63) / 64 * 64;
+        }
+        ws.pool.reserve(off * sizeof(bf16));
+        AB_CUDA(cudaMemsetAsync(ws.pool.p, 0, off * sizeof(bf16), st));
+    }
+    ws.n = n; ws.h = h; ws.w = w;
+}
+
+}  // namespace
+
+// prepared launch of one conv group in the forward direction.  `dst`/`dst_ctot`/`dst_c0`: where the result goes
+// (a level slice, a dense z tensor, or the f32 logits planes), `mode`/`act` as in tc.h.
+static void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const bf16* packs,
+                                   const float* P, std::vector<ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0, int mode, int act)
+{
+    out.assign(t.nlaunch, ConvLaunch());
+    const bool up = g.is_cont && g.stride == 2;
+    const int ol = g.out_level == -2 ? 0 : g.out_level;
+    // the M grid walks the SOURCE tensor's positions: same geometry as the output except for `up`
+    const Geo& grid = up ? ws.geo[g.in_level] : ws.geo[ol];
+    for (int l = 0; l < t.nlaunch; ++l) {
+        ConvSetup s;
+        if (g.in_level < 0) { s.src = ws.img.as<bf16>(); s.src_ctot = 8; s.a_c0 = 0; s.cin = 8; }
+        else if (g.pool_input) { s.src = ws.pool.as<bf16>() + ws.pool_off[&g - plan.groups.data()]; s.src_ctot = g.cin; s.a_c0 = 0; s.cin = g.cin; }
+        else { s.src = ws.level[g.in_level].as<bf16>(); s.src_ctot = plan.level_channels[g.in_level]; s.a_c0 = g.in_c0; s.cin = g.cin; }
+        s.src_positions = grid.positions();
+        s.packed = packs + t.fwd_pack_off[l];
+        s.ntaps = t.fwd_ntaps[l];
+        for (int i = 0; i < s.ntaps; ++i) { s.tap_dy[i] = t.fwd_tapdy[l][i]; s.tap_dx[i] = t.fwd_tapdx[l][i]; }
+        s.npad_total = t.npad;
+        s.grid = grid;
+        ConvLaunch& L = out[l];
+        tc::setup_conv(L, s);
+        L.mode = mode; L.act = act;
+        L.cout = g.cout;
+        L.out = dst; L.out_ctot = dst_ctot; L.out_c0 = dst_c0;
+        L.bias = P + g.b_off;
+        if (act != tc::ACT_NONE) { L.scale = P + g.bn_off; L.shift = P + g.bn_off + g.cout; }
+        if (up) {
+            L.mode = (mode == tc::OUT_BF16_ACCUM) ? tc::OUT_BF16_UP_ACCUM : tc::OUT_BF16_UP;
+            L.par_a = l / 2; L.par_b = l % 2;
+            L.out_S = ws.geo[ol].S(); L.out_P = ws.geo[ol].P();
+        }
+        const double px = (double)grid.N * grid.H * grid.W;
+        L.flops = 2.0 * px * g.cin * g.cout * s.ntaps;
+        L.bytes = 2.0 * px * (g.cin + g.cout) / (up ? 1.0 : 1.0);
+    }
+}
+
+void Engine::tc_ensure_infer(int h, int w)
+{
+    tc_pack_forward_filters();
+    TcState& T = *tc_;
+    if (T.iw.h == h && T.iw.w == w && T.iw.n == 1) return;
+    ensure_workspace(T.iw, plan_, 1, h, w, true, true, stream_);
+    i_logits_.reserve((size_t)plan_.class_count * h * w * sizeof(float));
+    const float* P = params_.as<float>();
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        TcGroup& t = T.groups[gi];
+        t.infer.clear();
+        if (g.dead) continue;
+        int act = tc::ACT_NONE;
+        if (g.dlib_bn >= 0) act = g.bn_first ? tc::ACT_AFFINE_MISH : tc::ACT_MISH_AFFINE;
+        if (g.out_level == -2)
+            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<bf16>(), P, t.infer, i_logits_.p, 0, 0, tc::OUT_F32_NCHW, act);
+        else
+            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<bf16>(), P, t.infer, T.iw.level[g.out_level].p,
+                                   plan_.level_channels[g.out_level], g.out_c0, tc::OUT_BF16, act);
+    }
+}
+
+void Engine::tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w)
+{
+    tc_ensure_infer(h, w);
+    tc::image_to_nhwc(img_dev, IH, IW, left, top, tc_->iw.img.as<bf16>(), tc_->iw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+}
+
+void Engine::tc_run_inference(int h, int w)
+{
+    if (model_.is_training) throw state_error("Forward needs a runtime net (anet_type); convert with GetRuntimeNet / as_runtime");
+    TcState& T = *tc_;
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        if (g.dead) continue;
+        if (g.pool_input)
+            tc::maxpool_nhwc(T.iw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.iw.geo[g.in_level],
+                             T.iw.pool.as<bf16>() + T.iw.pool_off[gi], T.iw.geo[g.out_level], stream_);
+        for (const ConvLaunch& L : T.groups[gi].infer) tc::launch_conv(L, stream_);
+    }
+    AB_CUDA(cudaGetLastError());
+}
+
+}  // namespace ab

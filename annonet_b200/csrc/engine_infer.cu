@@ -63,6 +63,11 @@ const float* Engine::forward_device(const uint8_t* img_dev, int h, int w)
 {
     if (!loaded_) throw state_error("no net loaded");
     AB_CUDA(cudaSetDevice(device_));
+    if (precision_ == 1) {  // AB_PRECISION_BF16: tcgen05 path
+        tc_input(img_dev, h, w, 0, 0, h, w);
+        tc_run_inference(h, w);
+        return i_logits_.as<float>();
+    }
     ensure_infer_ws(h, w);
     k::to_tensor(img_dev, i_x_.as<float>(), 1, h, w, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
     run_inference_graph(h, w);
@@ -119,9 +124,14 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
         const int cx = t.full[0] + fw / 2, cy = t.full[1] + fh / 2;
         const int rw = recommended_input_dimension(fw, plan_.levels), rh = recommended_input_dimension(fh, plan_.levels);
         const int left = cx - rw / 2, top = cy - rh / 2;
-        ensure_infer_ws(rh, rw);
-        k::extract_tile(img_dev, h, w, left, top, i_x_.as<float>(), rh, rw, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
-        run_inference_graph(rh, rw);
+        if (precision_ == 1) {
+            tc_input(img_dev, h, w, left, top, rh, rw);
+            tc_run_inference(rh, rw);
+        } else {
+            ensure_infer_ws(rh, rw);
+            k::extract_tile(img_dev, h, w, left, top, i_x_.as<float>(), rh, rw, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+            run_inference_graph(rh, rw);
+        }
         k::BlendArgs b;
         b.logits = i_logits_.as<float>(); b.K = K; b.th = rh; b.tw = rw;
         b.canvas = canvas_.as<float>(); b.H = h; b.W = w; b.left = left; b.top = top;

@@ -1,0 +1,95 @@
+// bf16 NHWC ("padded flat", see tc.h) elementwise / reduction kernels of the tensor-core path.
+// All are HBM-bound: 16-byte vector accesses of 8 channels, fp32 arithmetic.
+#include "kcommon.cuh"
+#include "tc.h"
+
+namespace ab {
+namespace tc {
+namespace {
+
+struct alignas(16) BF8 { __nv_bfloat162 v[4]; };
+
+__device__ __forceinline__ void unpack8(const BF8& b, float f[8])
+{
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(b.v[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ BF8 pack8(const float f[8])
+{
+    BF8 b;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) b.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return b;
+}
+
+__global__ void __launch_bounds__(256) image_to_nhwc_kernel(const uint8_t* __restrict__ img, int IH, int IW, int left, int top,
+                                                            bf16* __restrict__ out, int N, int H, int W, float ar, float ag, float ab_)
+{
+    const long long hw = (long long)H * W;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)N * hw) return;
+    const int n = (int)(i / hw);
+    const int rem = (int)(i - n * hw);
+    const int y = rem / W, x = rem - y * W;
+    const int sy = min(max(top + y, 0), IH - 1), sx = min(max(left + x, 0), IW - 1);
+    const uint8_t* p = img + ((long long)n * IH * IW + (long long)sy * IW + sx) * 3;
+    // (p - avg)/256 in double like input.h:96-115, then rounded once to bf16
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    f[0] = (float)(((double)p[0] - (double)ar) / 256.0);
+    f[1] = (float)(((double)p[1] - (double)ag) / 256.0);
+    f[2] = (float)(((double)p[2] - (double)ab_) / 256.0);
+    const long long S = (long long)(H + 1) * (W + 1);
+    const long long pos = n * S + (long long)(y + 1) * (W + 1) + (x + 1);
+    *reinterpret_cast<BF8*>(out + pos * 8) = pack8(f);
+}
+
+__global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const bf16* __restrict__ in, int in_ctot, int c0, int C8, int N, int Hi, int Wi,
+                                                           bf16* __restrict__ out, int Ho, int Wo)
+{
+    const long long total = (long long)N * Ho * Wo * C8;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int cg = (int)(i % C8);
+    long long p = i / C8;
+    const int x = (int)(p % Wo); p /= Wo;
+    const int y = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const long long Si = (long long)(Hi + 1) * (Wi + 1), So = (long long)(Ho + 1) * (Wo + 1);
+    float m[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const long long pi = n * Si + (long long)(2 * y + r + 1) * (Wi + 1) + (2 * x + q + 1);
+            float f[8];
+            unpack8(*reinterpret_cast<const BF8*>(in + pi * in_ctot + c0 + cg * 8), f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) m[k] = fmaxf(m[k], f[k]);
+        }
+    const long long po = n * So + (long long)(y + 1) * (Wo + 1) + (x + 1);
+    *reinterpret_cast<BF8*>(out + po * (C8 * 8) + cg * 8) = pack8(m);
+}
+
+}  // namespace
+
+void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* out, const Geo& g, float ar, float ag, float ab_,
+                   cudaStream_t st)
+{
+    const long long n = (long long)g.N * g.H * g.W;
+    k::ProfScope ps(k::F_INPUT, 0, 19.0 * n, st);
+    image_to_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(img, IH, IW, left, top, out, g.N, g.H, g.W, ar, ag, ab_);
+    k::count_launch();
+}
+
+void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st)
+{
+    const long long n = (long long)go.N * go.H * go.W * (C / 8);
+    k::ProfScope ps(k::F_EW_BF16, 0, 2.0 * C * ((double)gi.N * gi.H * gi.W + (double)go.N * go.H * go.W), st);
+    maxpool_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, in_ctot, c0, C / 8, gi.N, gi.H, gi.W, out, go.H, go.W);
+    k::count_launch();
+}
+
+}  // namespace tc
+}  // namespace ab

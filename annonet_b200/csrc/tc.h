@@ -1,0 +1,112 @@
+// bf16 tensor-core path (AB_PRECISION_BF16): tcgen05 / TMEM / TMA implicit-GEMM convolutions and the
+// bf16 NHWC kernels around them.
+//
+// Activation layout ("padded flat NHWC"): a tensor of N samples, H x W pixels, C channels is stored as
+//     bf16 [N*S + P + 1 positions][C],   P = W + 1,  S = (H + 1) * P,
+//     position(n, y, x) = n*S + (y + 1)*P + (x + 1),
+// i.e. every sample carries one zero row above it and every row one zero pixel to its left.  The pad to
+// the right of a row is the left pad of the next row, the pad below a sample is the top pad of the next
+// sample (or the P + 1 zero positions at the very end).  Producers never write pad positions, so they
+// stay zero from allocation on.  With that layout a 3x3 (or any) convolution is a GEMM over runs of 128
+// CONSECUTIVE positions whose tap (dy, dx) operand is the same run shifted by dy*P + dx positions: one
+// TMA-loaded halo segment in shared memory serves all nine taps through row-offset shared-memory
+// descriptors (the swizzle of tcgen05 descriptors is a function of the absolute shared address --
+// measured with experiments/umma_probe.cu -- so any row offset is legal).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace ab {
+namespace tc {
+
+typedef __nv_bfloat16 bf16;
+
+struct Geo {            // geometry of one padded flat tensor
+    int N = 0, H = 0, W = 0;
+    int P() const { return W + 1; }
+    long long S() const { return (long long)(H + 1) * (W + 1); }
+    long long positions() const { return (long long)N * S() + P() + 1; }  // allocated / tensor-map rows
+    long long pos(int n, int y, int x) const { return n * S() + (long long)(y + 1) * P() + (x + 1); }
+};
+
+enum OutMode {
+    OUT_BF16 = 0,        // out[pos][c0 + co] = act(acc + bias)            (same grid)
+    OUT_BF16_ACCUM = 1,  // out[pos][c0 + co] += acc                        (gradient accumulation)
+    OUT_F32_NCHW = 2,    // planes[n][co][y][x] = acc + bias                (class head -> logits)
+    OUT_BF16_UP = 3,     // out[fine pos (2r + a, 2c + b)][c0 + co] = acc + bias   (cont_ stride 2, one parity class)
+    OUT_BF16_UP_ACCUM = 4
+};
+enum Act { ACT_NONE = 0, ACT_MISH_AFFINE = 1, ACT_AFFINE_MISH = 2 };
+
+struct ConvLaunch {
+    alignas(64) CUtensorMap tmA;  // source positions x channels, box {kc, box_rows}
+    alignas(64) CUtensorMap tmB;  // packed filters [tap][npad_total][padded K], box {kc, nblk}
+    int a_c0 = 0;                 // first channel of the input slice
+    int nchunks = 0, kc = 16;     // K = nchunks * kc channels per tap (filters zero-padded beyond the real Cin)
+    int ntaps = 0;
+    // Tiling of the positions.  The tensor is a 2-D array of [N*(H+1) rows][P columns]; a CTA owns `th` M tiles of
+    // 128 positions: FLAT: consecutive runs (tile m starts at o0 + 128*m), one merged halo segment;
+    // ROWS: the same 128 columns of `th` consecutive rows (tile m starts at o0 + m*P), one 130-position
+    // segment per input row, shared by the three dy taps of three output rows.
+    int rows_mode = 0;
+    int ncx = 1;                  // ROWS: column tiles per row
+    int m_pos_stride = 128;       // position step between the M tiles of a CTA
+    int m_row_stride = 128;       // shared-memory row step between the M tiles of a CTA
+    int tap_row[9] = {0};         // shared-memory row of tap t for M tile 0
+    int nseg = 1;                 // segments per stage
+    int seg_pos[10] = {0};        // position of a segment's first row relative to o0
+    int seg_alloc = 0;            // rows reserved per segment (= nloads * box_rows)
+    int box_rows = 0, nloads = 0; // a segment = nloads TMA boxes of box_rows positions
+    int npad_total = 0, nblk = 0; // N of the GEMM (multiple of 16) and the part of it one CTA owns (<= 256)
+    int th = 1;                   // 128-position M tiles per CTA
+    int stages = 1;
+    int tmem_cols = 32;
+    unsigned smem_bytes = 0, a_stage_bytes = 0, stage_bytes = 0;
+    // geometry of the M grid (source/positions) and of the output
+    long long total = 0;          // N * S of the M grid
+    long long S = 0; int P = 0, H = 0, W = 0;
+    int mode = OUT_BF16, act = ACT_NONE;
+    int cout = 0;                 // real output channels (<= npad_total)
+    void* out = nullptr;          // bf16 [pos][out_ctot] or f32 planes
+    int out_ctot = 0, out_c0 = 0;
+    long long out_S = 0; int out_P = 0;  // fine grid (OUT_BF16_UP*)
+    int par_a = 0, par_b = 0;     // parity class of OUT_BF16_UP*
+    const float* bias = nullptr;  // [cout] or null
+    const float* scale = nullptr; // affine_/bn gamma-like and beta-like per channel (ACT_*)
+    const float* shift = nullptr;
+    long long grid_x = 0;         // CTAs along the positions
+    double flops = 0, bytes = 0;  // algorithmic work (for the profiler)
+};
+
+// host: fill tmA/tmB and the derived tiling fields.  src: bf16 [src_positions][src_ctot].
+struct ConvSetup {
+    const bf16* src = nullptr; long long src_positions = 0; int src_ctot = 0, a_c0 = 0, cin = 0;
+    const bf16* packed = nullptr;  // packed filters (see pack_filters_bf16)
+    int ntaps = 0; int tap_dy[9] = {0}, tap_dx[9] = {0};  // tap offset = dy*P + dx on the M grid
+    int npad_total = 0;
+    Geo grid;                      // geometry the M tiles walk over (the source tensor's)
+};
+int padded_k(int cin);             // multiple of 64
+int padded_n(int cout);            // multiple of 16
+size_t packed_filter_elems(int cin, int npad_total, int ntaps);
+void setup_conv(ConvLaunch& L, const ConvSetup& s);
+void launch_conv(const ConvLaunch& L, cudaStream_t st);
+
+// packed[tap][n][k] = (n < nreal && k < kreal) ? w[n*sn + k*sk + tapmap[tap]] : 0,   n < npad_total, k < padded_k(kreal)
+void pack_filters_bf16(const float* w, bf16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
+                       long long sk, cudaStream_t st);
+
+// ---- bf16 NHWC kernels around the convolutions (kernels_nhwc.cu) ---------------------------------
+// input_rgb_image::to_tensor (input.h:68-117) [+ tile extraction with clamp-to-edge, annonet_infer.cpp:68-75]:
+// u8 HWC images [N][IH][IW][3] -> padded flat NHWC with 8 channels (3 real + 5 zero); out pixel (y, x) of sample n
+// reads image pixel (clamp(top + y), clamp(left + x)).
+void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* out, const Geo& g, float ar, float ag, float ab_,
+                   cudaStream_t st);
+// max_pool_<3,3,2,2,0,0> (cpu_dlib.cpp:1888-1943): channels [c0, c0 + C) of `in` (geometry gi, ctot channels) -> dense
+// pooled tensor [positions of go][C]
+void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st);
+
+}  // namespace tc
+}  // namespace ab
