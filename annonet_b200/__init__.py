@@ -170,7 +170,7 @@ class _Net:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:  # (module globals are already gone at interpreter shutdown)
             lib.ab_net_destroy(h)
 
     @property

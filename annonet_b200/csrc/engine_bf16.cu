@@ -22,14 +22,20 @@ void forward_taps(const ConvGroup& g, TcGroup& t)
     if (g.ksize == 1) {
         t.fwd_ntaps[0] = 1;
         t.fwd_tapmap[0][0] = 0; t.fwd_tapdy[0][0] = 0; t.fwd_tapdx[0][0] = 0;
-    } else if (!g.is_cont) {           // con_ 3x3 s1 p1: out[y][x] += w[ky][kx] * in[y+ky-1][x+kx-1]
+    } else if (!g.is_cont) {           // con_ 3x3 s1 p1: out[y][x] += w[ky][kx] * in[y+ky-1][x+kx-1]; taps dx-major (tc.h "kym")
         t.fwd_ntaps[0] = 9;
-        for (int ky = 0; ky < 3; ++ky)
-            for (int kx = 0; kx < 3; ++kx) { const int i = ky * 3 + kx; t.fwd_tapmap[0][i] = i; t.fwd_tapdy[0][i] = ky - 1; t.fwd_tapdx[0][i] = kx - 1; }
+        for (int dx = -1; dx <= 1; ++dx)
+            for (int dy = -1; dy <= 1; ++dy) {
+                const int i = (dx + 1) * 3 + (dy + 1);
+                t.fwd_tapmap[0][i] = (dy + 1) * 3 + (dx + 1); t.fwd_tapdy[0][i] = dy; t.fwd_tapdx[0][i] = dx;
+            }
     } else if (g.stride == 1) {        // cont_ 3x3 s1 p1: out[Y][X] += w[ky][kx] * in[Y-ky+1][X-kx+1]   (layers.h:531)
         t.fwd_ntaps[0] = 9;
-        for (int ky = 0; ky < 3; ++ky)
-            for (int kx = 0; kx < 3; ++kx) { const int i = ky * 3 + kx; t.fwd_tapmap[0][i] = i; t.fwd_tapdy[0][i] = 1 - ky; t.fwd_tapdx[0][i] = 1 - kx; }
+        for (int dx = -1; dx <= 1; ++dx)
+            for (int dy = -1; dy <= 1; ++dy) {
+                const int i = (dx + 1) * 3 + (dy + 1);
+                t.fwd_tapmap[0][i] = (1 - dy) * 3 + (1 - dx); t.fwd_tapdy[0][i] = dy; t.fwd_tapdx[0][i] = dx;
+            }
     } else {
         // cont_ 3x3 s2 p0 ("up"): out[2r+a][2c+b] += w[ky][kx] * in[r + (a-ky)/2][c + (b-kx)/2] for ky = a (mod 2), kx = b (mod 2).
         // M position (r, c) of the coarse grid sits one row and one column before pixel (r, c): pixel (i, j) is at

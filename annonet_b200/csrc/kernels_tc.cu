@@ -48,20 +48,37 @@ __device__ __forceinline__ void tma_2d(uint32_t dst, const CUtensorMap* m, int c
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  ::"r"(dst), "l"(m), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
+// true in exactly one lane of the (converged) warp; ptxas treats the guarded region as single-threaded, so uniform-datapath
+// operands (tcgen05 / TMA descriptors) need no per-lane "waterfall" loop
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float v[16])
+// 16 consecutive fp32 accumulator columns of this thread's TMEM lane; results are valid after tmem_ld_wait()
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, float v[16])
 {
-    uint32_t r[16];
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]),
+                   "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
                  : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// ties the loaded registers to the wait so that no use of them can be scheduled ahead of it
+__device__ __forceinline__ void tmem_ld_fence(float v[16])
+{
+    asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]), "+f"(v[8]),
+                      "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]) :: "memory");
 }
 
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, LBO (unused for
@@ -73,7 +90,9 @@ __device__ __forceinline__ uint64_t smem_desc_hi(int pitch)
     return (sbo << 32) | (1ull << 46) | (layout << 61) | (1ull << 16);
 }
 
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = 32 * kEpiWarps;
+constexpr int kThreads = 64 + kEpiThreads;   // + TMA producer warp + MMA issuer warp
 constexpr int kMaxStages = 8;
 
 // D[tmem] (+)= A[smem desc] * B[smem desc]; descriptors assembled from 32-bit halves (hi is loop-invariant)
@@ -90,50 +109,48 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32
         "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 
-// mish for the bf16 path: x - 2x / (e^2 + 2e + 2) with the fast exp / divide (results are rounded to bf16 anyway)
+// mish for the bf16 path: x - 2x / (e^2 + 2e + 2), e = exp(x), on the raw MUFU approximations (results are rounded
+// to bf16 anyway).  e = inf -> rcp = 0 -> x;  e = 0 -> x - x = 0.
 __device__ __forceinline__ float mish_fast(float x)
 {
-    const float e = __expf(x);
-    return x - __fdividef(2.f * x, fmaf(e, e + 2.f, 2.f));
+    float e, rc;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(fmaf(e, e + 2.f, 2.f)));
+    return fmaf(-2.f * x, rc, x);
 }
 
+// Persistent, warp-specialised: one CTA per SM walks work items (a group of `th` M tiles x one N block) with a
+// shared-memory stage ring (TMA -> MMA) and two TMEM accumulator buffers (MMA -> epilogue), so the TMA loads, the
+// tensor-core work and the epilogue of consecutive items overlap.
 template <int NTAPS>
-__global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ ConvLaunch L)
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvLaunch L)
 {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], acc_bar;
+    __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_slot;
-    __shared__ __align__(16) float s_bias[256], s_scale[256], s_shift[256];
+    __shared__ __align__(16) float s_bias[512], s_scale[512], s_shift[512];
 
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pitch = L.kc * 2;
-    long long o0;
-    int cx = 0;
-    if (L.rows_mode) {
-        cx = (int)(blockIdx.x % L.ncx);
-        o0 = (long long)(blockIdx.x / L.ncx) * L.th * L.P + cx * 128;
-    } else {
-        o0 = (long long)blockIdx.x * (128 * L.th);
-    }
-    const int n0 = blockIdx.y * L.nblk;
+    const int grid_x = (int)L.grid_x, items = grid_x * (L.npad_total / L.nblk);   // (host checks that positions fit 31 bits)
+    const int nbuf = L.nbuf;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < L.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(&acc_bar, 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiThreads); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(L.tmem_cols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    if (warp >= 2) {  // per-channel epilogue parameters of this CTA's N block
-        for (int i = threadIdx.x - 64; i < L.nblk; i += 128) {
-            const int co = n0 + i;
+    if (warp >= 2) {  // per-channel epilogue parameters
+        for (int co = threadIdx.x - 64; co < L.npad_total; co += kEpiThreads) {
             const bool in = co < L.cout;
-            s_bias[i] = (in && L.bias) ? __ldg(L.bias + co) : 0.f;
-            s_scale[i] = (in && L.act != ACT_NONE) ? __ldg(L.scale + co) : 1.f;
-            s_shift[i] = (in && L.act != ACT_NONE) ? __ldg(L.shift + co) : 0.f;
+            s_bias[co] = (in && L.bias) ? __ldg(L.bias + co) : 0.f;
+            s_scale[co] = (in && L.act != ACT_NONE) ? __ldg(L.scale + co) : 1.f;
+            s_shift[co] = (in && L.act != ACT_NONE) ? __ldg(L.shift + co) : 0.f;
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -142,25 +159,31 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
     const uint32_t tmem = tmem_base_slot;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t tx = (uint32_t)(L.nseg * L.seg_alloc + NTAPS * L.nblk) * pitch;
-            for (int ch = 0; ch < L.nchunks; ++ch) {
-                const int s = ch % L.stages;
-                mbar_wait(&empty_bar[s], ((ch / L.stages) & 1) ^ 1);
-                mbar_expect(&full_bar[s], tx);
-                const uint32_t a_s = smem0 + (uint32_t)s * L.stage_bytes, b_s = a_s + L.a_stage_bytes;
-                const int c = L.a_c0 + ch * L.kc;
-                for (int sg = 0; sg < L.nseg; ++sg)
-                    for (int l = 0; l < L.nloads; ++l)
-                        tma_2d(a_s + (uint32_t)(sg * L.seg_alloc + l * L.box_rows) * pitch, &L.tmA, c,
-                               (int)(o0 + L.seg_pos[sg]) + l * L.box_rows, &full_bar[s]);
+            uint32_t it = 0;
+            for (int item = blockIdx.x; item < items; item += gridDim.x) {
+                const int by = item / grid_x, bx = item - by * grid_x;
+                const int n0 = by * L.nblk;
+                const int o0 = L.rows_mode ? (bx / L.ncx) * L.th * L.P + (bx % L.ncx) * 128 : bx * (128 * L.th);
+                for (int ch = 0; ch < L.nchunks; ++ch, ++it) {
+                    const int s = it % L.stages;
+                    mbar_wait(&empty_bar[s], ((it / L.stages) & 1) ^ 1);
+                    mbar_expect(&full_bar[s], tx);
+                    const uint32_t a_s = smem0 + (uint32_t)s * L.stage_bytes, b_s = a_s + L.a_stage_bytes;
+                    const int c = L.a_c0 + ch * L.kc;
+                    for (int sg = 0; sg < L.nseg; ++sg)
+                        for (int l = 0; l < L.nloads; ++l)
+                            tma_2d(a_s + (uint32_t)(sg * L.seg_alloc + l * L.box_rows) * pitch, &L.tmA, c,
+                                   o0 + L.seg_pos[sg] + l * L.box_rows, &full_bar[s]);
 #pragma unroll
-                for (int t = 0; t < NTAPS; ++t)
-                    tma_2d(b_s + (uint32_t)(t * L.nblk) * pitch, &L.tmB, ch * L.kc, t * L.npad_total + n0, &full_bar[s]);
+                    for (int t = 0; t < NTAPS; ++t)
+                        tma_2d(b_s + (uint32_t)(t * L.nblk) * pitch, &L.tmB, ch * L.kc, t * L.npad_total + n0, &full_bar[s]);
+                }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one()) {
             // instruction descriptor: D f32, A/B bf16, both K-major, N = nblk, M = 128
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(L.nblk >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t desc_hi = (uint32_t)(smem_desc_hi(pitch) >> 32);
@@ -174,98 +197,165 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
             }
             const uint32_t m_step = (uint32_t)(L.m_row_stride * pitch) >> 4;
             const uint32_t stage16 = L.stage_bytes >> 4, b_off16 = L.a_stage_bytes >> 4;
-            for (int ch = 0; ch < nchunks; ++ch) {
-                const int s = ch % stages;
-                mbar_wait(&full_bar[s], (ch / stages) & 1);
+            const int kym = L.kym;
+            const uint32_t row16 = (uint32_t)pitch >> 4, nb16 = (uint32_t)(nblk * pitch) >> 4;
+            uint32_t it = 0, ai = 0;
+            for (int item = blockIdx.x; item < items; item += gridDim.x, ++ai) {
+                const uint32_t buf = nbuf == 2 ? (ai & 1) : 0, use = ai / nbuf;
+                mbar_wait(&acc_empty[buf], (use & 1) ^ 1);   // the epilogue has drained this accumulator buffer
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t a0 = ((smem0 >> 4) + (uint32_t)s * stage16) | lbo, b0 = a0 + b_off16;
-                for (int m = 0; m < th; ++m) {
-                    const uint32_t am = a0 + (uint32_t)m * m_step, d = tmem + (uint32_t)(m * nblk);
+                const uint32_t tm = tmem + buf * (uint32_t)L.cols_buf;
+                for (int ch = 0; ch < nchunks; ++ch, ++it) {
+                    const int s = it % stages;
+                    mbar_wait(&full_bar[s], (it / stages) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t a0 = ((smem0 >> 4) + (uint32_t)s * stage16) | lbo, b0 = a0 + b_off16;
+                    if (NTAPS == 9 && kym) {
+                        // input row segment sg feeds output rows sg - u (u = dy + 1) of this item: u in [ulo, uhi]
+                        for (int sg = 0; sg < th + 2; ++sg) {
+                            const int ulo = max(0, sg - (th - 1)), uhi = min(2, sg);
+                            const uint32_t nn = (uint32_t)((uhi - ulo + 1) * nblk);
+                            const uint32_t idesc_n = (idesc & ~(0x3fu << 17)) | ((nn >> 3) << 17);
+                            const uint32_t d = tm + (uint32_t)((sg * 3 + ulo) * nblk);
+                            const uint32_t as = a0 + (uint32_t)sg * m_step;
 #pragma unroll
-                    for (int t = 0; t < NTAPS; ++t)
-                        for (int k = 0; k < ksteps; ++k)
-                            umma_bf16(d, am + tap_a[t] + 2 * k, b0 + tap_b[t] + 2 * k, desc_hi, idesc, (uint32_t)(ch | t | k));
+                            for (int dxi = 0; dxi < 3; ++dxi)
+                                for (int k = 0; k < ksteps; ++k)
+                                    umma_bf16(d, as + dxi * row16 + 2 * k, b0 + (uint32_t)(dxi * 3 + ulo) * nb16 + 2 * k, desc_hi, idesc_n,
+                                              (uint32_t)(ch | dxi | k));
+                        }
+                    } else {
+                        for (int m = 0; m < th; ++m) {
+                            const uint32_t am = a0 + (uint32_t)m * m_step, d = tm + (uint32_t)(m * nblk);
+#pragma unroll
+                            for (int t = 0; t < NTAPS; ++t)
+                                for (int k = 0; k < ksteps; ++k)
+                                    umma_bf16(d, am + tap_a[t] + 2 * k, b0 + tap_b[t] + 2 * k, desc_hi, idesc, (uint32_t)(ch | t | k));
+                        }
+                    }
+                    umma_commit(&empty_bar[s]);
                 }
-                umma_commit(&empty_bar[s]);
+                umma_commit(&acc_full[buf]);
             }
-            umma_commit(&acc_bar);
         }
     } else {
-        // ---- epilogue: thread <-> TMEM lane (position), 16 columns per tcgen05.ld
-        mbar_wait(&acc_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        // ---- epilogue (8 warps): thread <-> TMEM lane (position); warps 2-5 take the even M tiles, 6-9 the odd ones
+        const int q = warp & 3;              // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;    // which of every kEpiWarps/4 consecutive M tiles this warp takes
+        constexpr int kTileStep = kEpiWarps / 4;
         const bool up = L.mode == OUT_BF16_UP || L.mode == OUT_BF16_UP_ACCUM;
         const bool accum = L.mode == OUT_BF16_ACCUM || L.mode == OUT_BF16_UP_ACCUM;
-        const int act = L.act;
-        const bool col_ok = !L.rows_mode || cx * 128 + q * 32 + lane < L.P;
-        for (int m = 0; m < L.th; ++m) {
-            const long long pos = o0 + (long long)m * L.m_pos_stride + q * 32 + lane;
-            const int n = (int)(pos / L.S);
-            const int rem = (int)(pos - (long long)n * L.S);
-            const int r = rem / L.P, c = rem - r * L.P;
-            bool valid = pos < L.total && col_ok;
-            long long opos = pos;
-            if (up) {
-                // M grid = coarse tensor; row r <-> output rows 2r + a (r in [0, H] for a = 0, [0, H) for a = 1)
-                valid = valid && r <= L.H - L.par_a && c <= L.W - L.par_b;
-                opos = (long long)n * L.out_S + (long long)(2 * r + L.par_a + 1) * L.out_P + (2 * c + L.par_b + 1);
+        const int act = L.act, nblk = L.nblk, P = L.P, rows_per_sample = L.H + 1;
+        // position step between this thread's consecutive tiles (kTileStep M tiles), as rows + columns of the [rows][P] array
+        const int step_r = (kTileStep * L.m_pos_stride) / P, step_c = (kTileStep * L.m_pos_stride) % P;
+        uint32_t ai = 0;
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++ai) {
+            const int by = item / grid_x, bx = item - by * grid_x;
+            const int n0 = by * nblk;
+            // (sample, row, column) of this thread's first position; later tiles advance incrementally
+            int n, r, c, cx = 0;
+            if (L.rows_mode) {
+                const int rg = bx / L.ncx;
+                cx = bx - rg * L.ncx;
+                const int R = rg * L.th + half;            // global row of the [N*(H+1)][P] array
+                n = R / rows_per_sample; r = R - n * rows_per_sample;
+                c = cx * 128 + q * 32 + lane;
             } else {
-                valid = valid && r >= 1 && c >= 1;
+                const int pos0 = bx * (128 * L.th) + half * 128 + q * 32 + lane;
+                n = pos0 / (int)L.S;
+                const int rem = pos0 - n * (int)L.S;
+                r = rem / P; c = rem - r * P;
             }
-            for (int j = 0; j < L.nblk; j += 16) {
-                float v[16];
-                tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(m * L.nblk + j), v);
-                const int co0 = n0 + j;
-                if (!valid || co0 >= L.cout) continue;
-#pragma unroll
-                for (int i4 = 0; i4 < 4; ++i4) {
-                    const float4 b = *reinterpret_cast<const float4*>(&s_bias[j + 4 * i4]);
-                    v[4 * i4 + 0] += b.x; v[4 * i4 + 1] += b.y; v[4 * i4 + 2] += b.z; v[4 * i4 + 3] += b.w;
+            const bool col_ok = c < P;
+            const uint32_t buf = nbuf == 2 ? (ai & 1) : 0, use = ai / nbuf;
+            mbar_wait(&acc_full[buf], use & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tm = tmem + buf * (uint32_t)L.cols_buf + ((uint32_t)(q * 32) << 16);
+            for (int m = half; m < L.th; m += kTileStep) {
+                bool valid = n < L.Nsamples && col_ok;
+                long long opos;
+                if (up) {
+                    // M grid = coarse tensor; row r <-> output rows 2r + a (r in [0, H] for a = 0, [0, H) for a = 1)
+                    valid = valid && r <= L.H - L.par_a && c <= L.W - L.par_b;
+                    opos = (long long)n * L.out_S + (long long)(2 * r + L.par_a + 1) * L.out_P + (2 * c + L.par_b + 1);
+                } else {
+                    valid = valid && r >= 1 && c >= 1;
+                    opos = (long long)n * L.S + (long long)r * P + c;
                 }
-                if (act != ACT_NONE) {
+                for (int j = 0; j < nblk; j += 16) {
+                    float v[16];
+                    if (NTAPS == 9 && L.kym) {
+                        float w0[16], w1[16];
+                        tmem_ld16_issue(tm + (uint32_t)((m * 3 + 0) * nblk + j), v);
+                        tmem_ld16_issue(tm + (uint32_t)(((m + 1) * 3 + 1) * nblk + j), w0);
+                        tmem_ld16_issue(tm + (uint32_t)(((m + 2) * 3 + 2) * nblk + j), w1);
+                        tmem_ld_wait();
+                        tmem_ld_fence(v); tmem_ld_fence(w0); tmem_ld_fence(w1);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] += w0[i] + w1[i];
+                    } else {
+                        tmem_ld16_issue(tm + (uint32_t)(m * nblk + j), v);
+                        tmem_ld_wait();
+                        tmem_ld_fence(v);
+                    }
+                    const int co0 = n0 + j;
+                    if (!valid || co0 >= L.cout) continue;
 #pragma unroll
                     for (int i4 = 0; i4 < 4; ++i4) {
-                        const float4 sc = *reinterpret_cast<const float4*>(&s_scale[j + 4 * i4]);
-                        const float4 sh = *reinterpret_cast<const float4*>(&s_shift[j + 4 * i4]);
-                        const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            float& x = v[4 * i4 + e];
-                            x = act == ACT_MISH_AFFINE ? fmaf(mish_fast(x), scv[e], shv[e]) : mish_fast(fmaf(x, scv[e], shv[e]));
-                        }
+                        const float4 b = *reinterpret_cast<const float4*>(&s_bias[co0 + 4 * i4]);
+                        v[4 * i4 + 0] += b.x; v[4 * i4 + 1] += b.y; v[4 * i4 + 2] += b.z; v[4 * i4 + 3] += b.w;
                     }
-                }
-                if (L.mode == OUT_F32_NCHW) {
-                    const long long hw = (long long)L.H * L.W;
-                    float* o = (float*)L.out + ((long long)n * L.cout) * hw + (long long)(r - 1) * L.W + (c - 1);
+                    if (act != ACT_NONE) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (co0 + i < L.cout) o[(long long)(co0 + i) * hw] = v[i];
-                } else {
-                    // channel counts are multiples of 8: 16-byte vector stores of 8 channels
-                    bf16* o = (bf16*)L.out + opos * L.out_ctot + L.out_c0 + co0;
+                        for (int i4 = 0; i4 < 4; ++i4) {
+                            const float4 sc = *reinterpret_cast<const float4*>(&s_scale[co0 + 4 * i4]);
+                            const float4 sh = *reinterpret_cast<const float4*>(&s_shift[co0 + 4 * i4]);
+                            const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, shv[4] = {sh.x, sh.y, sh.z, sh.w};
 #pragma unroll
-                    for (int h8 = 0; h8 < 2; ++h8) {
-                        if (co0 + h8 * 8 >= L.cout) break;
-                        uint4* dst = reinterpret_cast<uint4*>(o + h8 * 8);
-                        __nv_bfloat162 pk[4];
-                        if (accum) {
-                            const uint4 old = *dst;
-                            const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&old);
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const float2 f = __bfloat1622float2(ob[i]);
-                                pk[i] = __floats2bfloat162_rn(f.x + v[h8 * 8 + 2 * i], f.y + v[h8 * 8 + 2 * i + 1]);
+                            for (int e = 0; e < 4; ++e) {
+                                float& x = v[4 * i4 + e];
+                                x = act == ACT_MISH_AFFINE ? fmaf(mish_fast(x), scv[e], shv[e]) : mish_fast(fmaf(x, scv[e], shv[e]));
                             }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) pk[i] = __floats2bfloat162_rn(v[h8 * 8 + 2 * i], v[h8 * 8 + 2 * i + 1]);
                         }
-                        *dst = *reinterpret_cast<const uint4*>(pk);
+                    }
+                    if (L.mode == OUT_F32_NCHW) {
+                        const long long hw = (long long)L.H * L.W;
+                        float* o = (float*)L.out + ((long long)n * L.cout) * hw + (long long)(r - 1) * L.W + (c - 1);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (co0 + i < L.cout) o[(long long)(co0 + i) * hw] = v[i];
+                    } else {
+                        // channel counts are multiples of 8: 16-byte vector stores of 8 channels
+                        bf16* o = (bf16*)L.out + opos * L.out_ctot + L.out_c0 + co0;
+#pragma unroll
+                        for (int h8 = 0; h8 < 2; ++h8) {
+                            if (co0 + h8 * 8 >= L.cout) break;
+                            uint4* dst = reinterpret_cast<uint4*>(o + h8 * 8);
+                            __nv_bfloat162 pk[4];
+                            if (accum) {
+                                const uint4 old = *dst;
+                                const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&old);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const float2 f = __bfloat1622float2(ob[i]);
+                                    pk[i] = __floats2bfloat162_rn(f.x + v[h8 * 8 + 2 * i], f.y + v[h8 * 8 + 2 * i + 1]);
+                                }
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) pk[i] = __floats2bfloat162_rn(v[h8 * 8 + 2 * i], v[h8 * 8 + 2 * i + 1]);
+                            }
+                            *dst = *reinterpret_cast<const uint4*>(pk);
+                        }
                     }
                 }
+                // next tile of this thread
+                c += step_c; r += step_r;
+                if (c >= P) { c -= P; ++r; }
+                while (r >= rows_per_sample) { r -= rows_per_sample; ++n; }
             }
+            // this thread's TMEM reads of the buffer are complete (tcgen05.wait::ld in tmem_ld16): hand it back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty[buf])) : "memory");
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -305,14 +395,14 @@ EncodeTiledFn encode_fn()
     return fn;
 }
 
-void make_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int kc, int box_rows)
+void make_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int kc, int box_rows, CUtensorMapL2promotion promo)
 {
     cuuint64_t dims[2] = {(cuuint64_t)ctot, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)ctot * 2};
     cuuint32_t box[2] = {(cuuint32_t)kc, (cuuint32_t)box_rows}, es[2] = {1, 1};
     const CUtensorMapSwizzle sw = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
     const CUresult r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
-                                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         throw std::runtime_error("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + "): rows " + std::to_string(rows) + " ctot " +
                                  std::to_string(ctot) + " kc " + std::to_string(kc) + " box_rows " + std::to_string(box_rows));
@@ -350,9 +440,10 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     L.nblk = ((s.npad_total + nblocks - 1) / nblocks + 15) / 16 * 16;
     nblocks = (s.npad_total + L.nblk - 1) / L.nblk;
     if (nblocks * L.nblk != s.npad_total) throw std::logic_error("N blocks must tile the padded N");
+    if (s.grid.positions() + 4096 >= (1ll << 31)) throw std::invalid_argument("tensor too large for the bf16 conv kernel (positions must fit 31 bits)");
     const int P = s.grid.P();
     L.total = (long long)s.grid.N * s.grid.S();
-    L.S = s.grid.S(); L.P = P; L.H = s.grid.H; L.W = s.grid.W;
+    L.S = s.grid.S(); L.P = P; L.H = s.grid.H; L.W = s.grid.W; L.Nsamples = s.grid.N;
     int dylo = 0, dyhi = 0, dxlo = 0, dxhi = 0, lo = 0, hi = 0;
     for (int t = 0; t < s.ntaps; ++t) {
         dylo = std::min(dylo, s.tap_dy[t]); dyhi = std::max(dyhi, s.tap_dy[t]);
@@ -360,6 +451,9 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
         const int off = s.tap_dy[t] * P + s.tap_dx[t];
         lo = std::min(lo, off); hi = std::max(hi, off);
     }
+    bool kym_ok = s.ntaps == 9 && nblocks == 1;
+    for (int t = 0; t < s.ntaps && kym_ok; ++t) kym_ok = s.tap_dx[t] == t / 3 - 1 && s.tap_dy[t] == t % 3 - 1;
+    static const bool no_kym = getenv("AB_TC_NO_KYM") != nullptr;
     const long long rows_total = (long long)s.grid.N * (s.grid.H + 1);
     const long long tiles_flat = (L.total + 127) / 128;
     const int ncx = (P + 127) / 128;
@@ -367,12 +461,18 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     // candidate search: K chunk, tiling mode, M tiles per CTA (see the cost model in DESIGN.md)
     struct Cand { double cost; int kc, rows_mode, th, nseg, seg_rows, nloads, box_rows, stages; unsigned a_bytes, stage_bytes; long long ctas; };
     Cand best{1e300, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    static const int force_kc = getenv("AB_TC_KC") ? atoi(getenv("AB_TC_KC")) : 0, force_th = getenv("AB_TC_TH") ? atoi(getenv("AB_TC_TH")) : 0;
+    static const int force_mode = getenv("AB_TC_MODE") ? atoi(getenv("AB_TC_MODE")) : -1;
     for (int kc : {16, 32, 64}) {
+        if (force_kc && kc != force_kc && s.cin >= force_kc) continue;
         const int kpad = (s.cin + kc - 1) / kc * kc, nchunks = kpad / kc, pitch = kc * 2;
-        for (int rows_mode = 0; rows_mode < 2; ++rows_mode) {
+        for (int rows_mode = 0; rows_mode < 3; ++rows_mode) {   // 0 FLAT, 1 ROWS, 2 ROWS + merged dy taps
             if (rows_mode && P < 128) continue;
+            if (rows_mode == 2 && (!kym_ok || no_kym)) continue;
+            if (force_mode >= 0 && rows_mode != force_mode && P >= 128) continue;
             for (int th : {8, 4, 2, 1}) {
-                if (th * L.nblk > 512) continue;
+                if (rows_mode == 2 && th < 2) continue;
+                if (force_th && th > force_th) continue;
                 const int nseg = rows_mode ? th + dyhi - dylo : 1;
                 if (nseg > 10) continue;
                 const int seg_rows = rows_mode ? 128 + dxhi - dxlo : 128 * th + hi - lo;
@@ -380,17 +480,36 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
                 const int box_rows = ((seg_rows + nloads - 1) / nloads + 7) / 8 * 8;
                 const unsigned a_bytes = (unsigned)(((size_t)nseg * nloads * box_rows * pitch + 1023) / 1024 * 1024);
                 const unsigned stage = a_bytes + (unsigned)(((size_t)s.ntaps * L.nblk * pitch + 1023) / 1024 * 1024);
-                const size_t budget = (th * L.nblk <= 256 ? 100u : 200u) * 1024u;
+                const int cols_needed = (rows_mode == 2 ? (th + 2) * 3 : th) * L.nblk;
+                if (cols_needed > 512) continue;
+                const bool two = cols_needed <= 256;   // double-buffered accumulators: MMAs of item i+1 overlap the epilogue of item i
+                const size_t budget = 200u * 1024u;
                 const int want = std::min(nchunks, 2);
                 if ((size_t)stage * want + 1024 > budget) continue;
-                const int stages = (int)std::min<size_t>(std::min(nchunks, kMaxStages), (budget - 1024) / stage);
+                const int stages = (int)std::min<size_t>(kMaxStages, (budget - 1024) / stage);
                 const long long ctas = rows_mode ? ((rows_total + th - 1) / th) * ncx : (tiles_flat + th - 1) / th;
                 const double waste = rows_mode ? (double)ncx * 128 / P * ((double)((rows_total + th - 1) / th) * th / rows_total)
                                                : (double)((tiles_flat + th - 1) / th) * th / tiles_flat;
                 const double loadf = (double)nseg * nloads * box_rows / (128.0 * th);
-                double cost = waste * kpad * (s.ntaps + 1.0 * loadf);
-                if (ctas < k::kNumSMs) cost *= (double)k::kNumSMs / ctas;
-                cost *= 1.0 + 0.02 * (kc == 16 ? 2 : kc == 32 ? 1 : 0);  // ties: fewer, larger TMA boxes
+                // cycle model of one work item on one SM (measured constants: experiments/umma_bench.cu, tma_bench.cu):
+                //   tcgen05.mma M128 K16: 32 + N/4 cycles (shared-memory operand reads) or N/2 (tensor pipe);  TMA: ~2.4 cycles
+                //   per box row with every SM loading;  epilogue: ~600 cycles per 128 x 16 accumulator block.
+                const int ksteps = kc / 16;
+                auto mma_cyc = [](int n) { return std::max(32.0 + n / 4.0, n / 2.0); };
+                double t_mma;
+                if (rows_mode == 2) {
+                    t_mma = 0;
+                    for (int sg = 0; sg < th + 2; ++sg)
+                        t_mma += 3.0 * ksteps * mma_cyc((std::min(2, sg) - std::max(0, sg - (th - 1)) + 1) * L.nblk);
+                } else t_mma = (double)th * s.ntaps * ksteps * mma_cyc(L.nblk);
+                t_mma *= nchunks;
+                const double t_tma = 2.4 * nchunks * ((double)nseg * nloads * box_rows + (double)s.ntaps * L.nblk);
+                const double t_epi = 600.0 * th * (L.nblk / 16) * (rows_mode == 2 ? 1.15 : 1.0);
+                const double t_item = two ? std::max(std::max(t_mma, t_tma), t_epi) : std::max(t_tma, t_mma + t_epi);
+                const long long rounds = (ctas * nblocks + k::kNumSMs - 1) / k::kNumSMs;
+                (void)waste; (void)loadf;
+                double cost = (double)rounds * t_item + 3000.0;   // + pipeline fill / drain
+                cost *= 1.0 + 0.01 * (kc == 16 ? 2 : kc == 32 ? 1 : 0);  // ties: fewer, larger TMA boxes
                 if (cost < best.cost) best = Cand{cost, kc, rows_mode, th, nseg, seg_rows, nloads, box_rows, stages, a_bytes, stage, ctas};
             }
         }
@@ -398,7 +517,7 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     if (best.kc == 0) throw std::logic_error("no tcgen05 conv tiling fits shared memory");
     L.kc = best.kc;
     L.nchunks = (s.cin + L.kc - 1) / L.kc;
-    L.rows_mode = best.rows_mode; L.th = best.th; L.nseg = best.nseg; L.nloads = best.nloads; L.box_rows = best.box_rows;
+    L.rows_mode = best.rows_mode != 0; L.kym = best.rows_mode == 2; L.th = best.th; L.nseg = best.nseg; L.nloads = best.nloads; L.box_rows = best.box_rows;
     L.seg_alloc = best.nloads * best.box_rows;
     L.a_stage_bytes = best.a_bytes; L.stage_bytes = best.stage_bytes; L.stages = std::max(best.stages, 1);
     L.smem_bytes = L.stages * L.stage_bytes + 1024;
@@ -412,16 +531,19 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
         L.seg_pos[0] = lo;
         for (int t = 0; t < s.ntaps; ++t) L.tap_row[t] = s.tap_dy[t] * P + s.tap_dx[t] - lo;
     }
+    L.cols_buf = (L.kym ? (L.th + 2) * 3 : L.th) * L.nblk;
+    L.nbuf = L.cols_buf <= 256 ? 2 : 1;
     int cols = 32;
-    while (cols < L.th * L.nblk) cols *= 2;
+    while (cols < L.nbuf * L.cols_buf) cols *= 2;
     L.tmem_cols = cols;
     L.grid_x = best.ctas;
     static const bool debug = getenv("AB_TC_DEBUG") != nullptr;
     if (debug)
         fprintf(stderr, "tc conv: P %d cin %d npad %d taps %d -> kc %d %s th %d nseg %d seg %d stages %d smem %u ctas %lld cost %.1f\n", P, s.cin,
-                s.npad_total, s.ntaps, L.kc, L.rows_mode ? "ROWS" : "FLAT", L.th, L.nseg, L.seg_alloc, L.stages, L.smem_bytes, best.ctas, best.cost);
-    make_map_2d(&L.tmA, s.src, s.src_positions, s.src_ctot, L.kc, L.box_rows);
-    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * s.npad_total, padded_k(s.cin), L.kc, L.nblk);
+                s.npad_total, s.ntaps, L.kc, L.kym ? "KYM" : L.rows_mode ? "ROWS" : "FLAT", L.th, L.nseg, L.seg_alloc, L.stages, L.smem_bytes, best.ctas, best.cost);
+    // activations: 64-byte L2 promotion -- a narrow channel slice costs 64 B of HBM traffic per position instead of 128 (experiments/tma_bench.cu)
+    make_map_2d(&L.tmA, s.src, s.src_positions, s.src_ctot, L.kc, L.box_rows, L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * s.npad_total, padded_k(s.cin), L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
 }
 
 template <int NTAPS>
@@ -432,8 +554,8 @@ static void launch_conv_t(const ConvLaunch& L, cudaStream_t st)
         cudaFuncSetAttribute(conv_tc_kernel<NTAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         attr_set = true;
     }
-    dim3 grid((unsigned)L.grid_x, (unsigned)(L.npad_total / L.nblk));
-    conv_tc_kernel<NTAPS><<<grid, kThreads, L.smem_bytes, st>>>(L);
+    const long long items = L.grid_x * (L.npad_total / L.nblk);
+    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::kNumSMs), kThreads, L.smem_bytes, st>>>(L);
 }
 
 void launch_conv(const ConvLaunch& L, cudaStream_t st)

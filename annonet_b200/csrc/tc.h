@@ -51,6 +51,10 @@ struct ConvLaunch {
     // ROWS: the same 128 columns of `th` consecutive rows (tile m starts at o0 + m*P), one 130-position
     // segment per input row, shared by the three dy taps of three output rows.
     int rows_mode = 0;
+    // ROWS + merged dy taps ("kym", 3x3 only, taps ordered dx-major): one accumulator tile PER INPUT ROW holding the
+    // partial sums of its three dy taps side by side (N = 3*npad), three MMAs (one per dx) per input row and K step
+    // instead of nine per output row; the epilogue adds the three row partials (same TMEM lane, no data movement).
+    int kym = 0;
     int ncx = 1;                  // ROWS: column tiles per row
     int m_pos_stride = 128;       // position step between the M tiles of a CTA
     int m_row_stride = 128;       // shared-memory row step between the M tiles of a CTA
@@ -62,11 +66,12 @@ struct ConvLaunch {
     int npad_total = 0, nblk = 0; // N of the GEMM (multiple of 16) and the part of it one CTA owns (<= 256)
     int th = 1;                   // 128-position M tiles per CTA
     int stages = 1;
-    int tmem_cols = 32;
+    int tmem_cols = 32;           // allocated TMEM columns (power of two)
+    int cols_buf = 0, nbuf = 1;   // accumulator columns of one work item; 2 buffers when they fit
     unsigned smem_bytes = 0, a_stage_bytes = 0, stage_bytes = 0;
     // geometry of the M grid (source/positions) and of the output
     long long total = 0;          // N * S of the M grid
-    long long S = 0; int P = 0, H = 0, W = 0;
+    long long S = 0; int P = 0, H = 0, W = 0, Nsamples = 0;
     int mode = OUT_BF16, act = ACT_NONE;
     int cout = 0;                 // real output channels (<= npad_total)
     void* out = nullptr;          // bf16 [pos][out_ctot] or f32 planes
