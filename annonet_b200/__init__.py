@@ -55,10 +55,10 @@ class _Tile(C.Structure):
 # every symbol include/annonet_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
-    "ab_net_init_random", "ab_net_load_dlib", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
+    "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
     "ab_infer_tiled_partial", "ab_infer_finish", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
-    "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_layer_gradient", "ab_get_layer_params",
+    "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
 ]
@@ -330,6 +330,13 @@ class TrainingNet(_Net):
         n, h, w = self._shape
         out = np.empty((n, self.info()["class_count"], h, w), dtype=np.float32)
         _check(lib.ab_get_logits(self._h, _ptr(out), C.c_size_t(out.size)))
+        return out
+
+    def level_tensor(self, level: int, gradient: bool = False) -> np.ndarray:
+        dims = (C.c_int32 * 4)()
+        _check(lib.ab_get_level_tensor(self._h, level, int(gradient), None, C.c_size_t(0), dims))
+        out = np.empty(tuple(dims), dtype=np.float32)
+        _check(lib.ab_get_level_tensor(self._h, level, int(gradient), _ptr(out), C.c_size_t(out.size), dims))
         return out
 
     def layer_gradient(self, idx: int) -> np.ndarray:

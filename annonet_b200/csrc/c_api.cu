@@ -99,6 +99,14 @@ ab_status ab_net_load_dlib(ab_net* net, const void* bytes, size_t n)
     return guarded([&] { E(net).load(ab::parse_net(bytes, n)); });
 }
 
+ab_status ab_net_load_dlib_prefix(ab_net* net, const void* bytes, size_t n, size_t* consumed)
+{
+    return guarded([&] {
+        if (!consumed) throw std::invalid_argument("consumed must not be null");
+        E(net).load(ab::parse_net(bytes, n, 6, consumed));
+    });
+}
+
 ab_status ab_net_save_dlib(ab_net* net, int as_runtime, void** bytes, size_t* n)
 {
     return guarded([&] {
@@ -265,6 +273,20 @@ ab_status ab_get_logits(ab_net* net, float* out, size_t capacity_floats)
         if (capacity_floats < n) throw std::invalid_argument("logits buffer too small");
         e.synchronize();
         AB_CUDA(cudaMemcpy(out, e.train_logits(), n * sizeof(float), cudaMemcpyDeviceToHost));
+    });
+}
+
+ab_status ab_get_level_tensor(ab_net* net, int level, int gradient, float* out, size_t capacity_floats, int32_t dims[4])
+{
+    return guarded([&] {
+        std::vector<float> v;
+        int d[4];
+        E(net).level_values(level, gradient != 0, v, d);
+        for (int i = 0; i < 4; ++i) dims[i] = d[i];
+        if (out) {
+            if (capacity_floats < v.size()) throw std::invalid_argument("level buffer too small");
+            std::memcpy(out, v.data(), v.size() * sizeof(float));
+        }
     });
 }
 

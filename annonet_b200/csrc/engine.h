@@ -88,6 +88,8 @@ public:
     float* grads() const { return grads_.as<float>(); }
     float* params() const { return params_.as<float>(); }
     void layer_values(int dlib_layer, bool gradient, std::vector<float>& out);  // dlib layout
+    // all tensors of one resolution level after the last training step (activations or their gradients), NCHW fp32
+    void level_values(int level, bool gradient, std::vector<float>& out, int dims[4]);
 
     void comm_init(const void* id128, int rank, int world);
     int world() const { return world_; }

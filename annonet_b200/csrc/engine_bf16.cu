@@ -97,8 +97,6 @@ void Engine::tc_pack_forward_filters()
     T.fwd_packs_valid = true;
 }
 
-namespace {
-
 // workspace of padded flat NHWC level buffers for n samples of h x w
 void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, cudaStream_t st)
 {
@@ -130,11 +128,9 @@ void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bo
     ws.n = n; ws.h = h; ws.w = w;
 }
 
-}  // namespace
-
 // prepared launch of one conv group in the forward direction.  `dst`/`dst_ctot`/`dst_c0`: where the result goes
 // (a level slice, a dense z tensor, or the f32 logits planes), `mode`/`act` as in tc.h.
-static void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const bf16* packs,
+void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const bf16* packs,
                                    const float* P, std::vector<ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0, int mode, int act)
 {
     out.assign(t.nlaunch, ConvLaunch());

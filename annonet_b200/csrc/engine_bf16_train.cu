@@ -1,0 +1,369 @@
+// Training step of the bf16 tensor-core path (AB_PRECISION_BF16): the dnn_trainer step of engine_train.cu
+// (trainer.h:631-671,743-828) over padded flat NHWC bf16 tensors (tc.h).
+//   forward : conv (tcgen05, kernels_tc.cu) -> z [fp32] -> batch statistics -> bn/mish -> level slice
+//   loss    : fp32 logits planes (the head conv writes them directly) -> loss + gradient (kernels_misc.cu)
+//   backward: bn/mish backward (z, gy -> dz [bf16], + bias gradient) -> filter gradient (kernels_wgrad_mma.cu)
+//             -> backward-data as a tcgen05 conv with transposed filters accumulating into the gradient level slice
+//   update  : fp32 master parameters / fp32 gradient arena, the same fused SGD/Adam kernel as the fp32 path;
+//             the bf16 filter packs of both directions are rebuilt from the master copy by one batched kernel.
+#include "engine.h"
+#include "tc_state.h"
+
+#include <cstring>
+
+namespace ab {
+
+using tc::bf16;
+using tc::ConvLaunch;
+using tc::ConvSetup;
+using tc::Geo;
+using tc::View;
+
+namespace {
+
+// N of a backward-data GEMM (= cin of the group) padded so that the <= 256 wide N blocks of setup_conv tile it
+int tiled_n(int c)
+{
+    const int npad = tc::padded_n(c);
+    const int nblocks = (npad + 255) / 256;
+    const int nblk = ((npad + nblocks - 1) / nblocks + 15) / 16 * 16;
+    return nblocks * nblk;
+}
+
+// taps of the backward-data convolution of a group: gin[pos][ci] += sum_t dz[pos + (dy, dx)_t][co] * w(t)[ci][co]
+void backward_taps(const ConvGroup& g, TcGroup& t)
+{
+    if (g.ksize == 1) {
+        t.bwd_ntaps = 1;
+        t.bwd_tapmap[0] = 0; t.bwd_tapdy[0] = 0; t.bwd_tapdx[0] = 0;
+        return;
+    }
+    t.bwd_ntaps = 9;
+    for (int dx = -1; dx <= 1; ++dx)
+        for (int dy = -1; dy <= 1; ++dy) {
+            const int i = (dx + 1) * 3 + (dy + 1);   // dx-major: the order the merged-dy-tap mode of the kernel wants
+            t.bwd_tapdy[i] = dy; t.bwd_tapdx[i] = dx;
+            if (!g.is_cont)               // con_: gin[y][x] += dz[y - ky + 1][x - kx + 1] * w[co][ci][ky][kx]   (layers.h:217)
+                t.bwd_tapmap[i] = (1 - dy) * 3 + (1 - dx);
+            else                          // cont_ s1: gin[y][x] += dz[y + ky - 1][x + kx - 1] * w[ci][co][ky][kx] (layers.h:542)
+                t.bwd_tapmap[i] = (dy + 1) * 3 + (dx + 1);   // cont_ s2 on the fine grid, evaluated at pixel (2i + 1, 2j + 1): the same
+        }
+}
+
+}  // namespace
+
+void Engine::tc_ensure_train(int n, int h, int w)
+{
+    if (!tc_) tc_ = std::make_unique<TcState>();
+    TcState& T = *tc_;
+    if (T.train_ready && T.tw.n == n && T.tw.h == h && T.tw.w == w) return;
+    synchronize();
+    T.train_ready = false;
+    // group table + forward pack offsets (shared with the inference path)
+    T.fwd_packs_valid = false;
+    tc_pack_forward_filters();
+    const int K = plan_.class_count;
+    if (K > 8) throw std::invalid_argument("the bf16 training path supports at most 8 classes in this build");
+    ensure_workspace(T.tw, plan_, n, h, w, true, true, stream_);
+    ensure_workspace(T.tg, plan_, n, h, w, false, false, stream_);
+    t_logits_.reserve((size_t)n * K * h * w * 4);
+    t_glogits_.reserve((size_t)n * K * h * w * 4);
+    t_loss_.reserve(sizeof(double));
+
+    // per group buffers
+    size_t z_elems = 0, dpool_elems = 0, upx_elems = 0, bwd_elems = 0, stt = 0;
+    int cmax = 8;
+    stats_off_.assign(plan_.groups.size(), 0);
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        TcGroup& t = T.groups[gi];
+        const int ol = g.out_level == -2 ? 0 : g.out_level;
+        cmax = std::max(cmax, g.cout);
+        if (g.dlib_bn >= 0) {
+            stats_off_[gi] = stt; stt += 2 * (size_t)g.cout;
+            t.z_off = z_elems;
+            z_elems += ((size_t)T.tw.geo[ol].positions() * g.cout + 63) / 64 * 64;
+        }
+        if (g.dead) continue;
+        if (g.pool_input) { t.dpool_off = dpool_elems; dpool_elems += ((size_t)T.tw.geo[ol].positions() * g.cin + 63) / 64 * 64; }
+        if (g.is_cont && g.stride == 2) { t.upx_off = upx_elems; upx_elems += ((size_t)T.tw.geo[ol].positions() * g.cin + 63) / 64 * 64; }
+        if (g.in_level >= 0) {
+            backward_taps(g, t);
+            t.bwd_npad = tiled_n(g.cin);
+            t.bwd_pack_off = bwd_elems;
+            bwd_elems += (tc::packed_filter_elems(std::max(g.cout, 8), t.bwd_npad, t.bwd_ntaps) + 511) / 512 * 512;
+        }
+    }
+    auto zero_reserve = [&](DevBuf& b, size_t bytes) {
+        b.reserve(std::max<size_t>(bytes, 256));
+        AB_CUDA(cudaMemsetAsync(b.p, 0, std::max<size_t>(bytes, 256), stream_));
+    };
+    zero_reserve(T.z, z_elems * 4);
+    zero_reserve(T.dz, z_elems * 2);
+    zero_reserve(T.dpool, dpool_elems * 2);
+    zero_reserve(T.upx, upx_elems * 2);
+    zero_reserve(T.glogits16, (size_t)T.tw.geo[0].positions() * 8 * 2);
+    zero_reserve(T.bwd_packs, bwd_elems * 2);
+    T.sums.reserve(sizeof(double) * 2 * cmax);
+    T.bias_tmp.reserve(sizeof(float) * 256);
+    T.wscratch.reserve(tc::wgrad_mma_scratch_floats() * 4);
+    t_stats_.reserve(std::max<size_t>(stt, 1) * 4);
+
+    // filter-pack jobs: every forward launch and every backward-data conv, rebuilt from the fp32 arena each step
+    std::vector<tc::PackJob> jobs;
+    T.max_pack_elems = 0;
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        const TcGroup& t = T.groups[gi];
+        const int kk = g.ksize * g.ksize;
+        for (int l = 0; l < t.nlaunch; ++l) {
+            tc::PackJob j{};
+            j.w_off = (long long)g.w_off; j.packed_off = (long long)t.fwd_pack_off[l];
+            j.sn = g.is_cont ? kk : (long long)g.cin * kk; j.sk = g.is_cont ? (long long)g.cout * kk : kk;
+            j.nreal = g.cout; j.npad = t.npad; j.kreal = g.cin; j.kp = tc::padded_k(g.in_level < 0 ? 8 : g.cin); j.ntaps = t.fwd_ntaps[l];
+            for (int i = 0; i < j.ntaps; ++i) j.tapmap[i] = t.fwd_tapmap[l][i];
+            T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp);
+            jobs.push_back(j);
+        }
+    }
+    T.n_fwd_jobs = (int)jobs.size();
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        const TcGroup& t = T.groups[gi];
+        const int kk = g.ksize * g.ksize;
+        if (g.dead || g.in_level < 0) continue;
+        tc::PackJob j{};
+        j.w_off = (long long)g.w_off; j.packed_off = (long long)t.bwd_pack_off;
+        // n = ci, k = co:  con_ [co][ci][kk], cont_ [ci][co][kk]
+        j.sn = g.is_cont ? (long long)g.cout * kk : kk; j.sk = g.is_cont ? kk : (long long)g.cin * kk;
+        j.nreal = g.cin; j.npad = t.bwd_npad; j.kreal = g.cout; j.kp = tc::padded_k(std::max(g.cout, 8)); j.ntaps = t.bwd_ntaps;
+        for (int i = 0; i < j.ntaps; ++i) j.tapmap[i] = t.bwd_tapmap[i];
+        T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp);
+        jobs.push_back(j);
+    }
+    T.n_pack_jobs = (int)jobs.size();
+    T.pack_jobs.reserve(jobs.size() * sizeof(tc::PackJob));
+    AB_CUDA(cudaMemcpyAsync(T.pack_jobs.p, jobs.data(), jobs.size() * sizeof(tc::PackJob), cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaStreamSynchronize(stream_));   // `jobs` is a local
+
+    // launches
+    const float* P = params_.as<float>();
+    float* G = grads_.as<float>();
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        TcGroup& t = T.groups[gi];
+        const int ol = g.out_level == -2 ? 0 : g.out_level;
+        const bool up = g.is_cont && g.stride == 2;
+        float* z = T.z.as<float>() + t.z_off;
+        // forward: conv (+ bias) -> z, the logits planes, or (`up`) the destination slice
+        if (g.dlib_bn >= 0)
+            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, z, g.cout, 0, tc::OUT_F32_NHWC, tc::ACT_NONE);
+        else if (g.out_level == -2)
+            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, t_logits_.p, 0, 0, tc::OUT_F32_NCHW, tc::ACT_NONE);
+        else
+            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, T.tw.level[g.out_level].p,
+                                   plan_.level_channels[g.out_level], g.out_c0, tc::OUT_BF16, tc::ACT_NONE);
+        t.dgrad.clear();
+        if (g.dead) continue;
+
+        // gradient at the conv output: dz (in z's place), the loss gradient, or the gradient slice itself
+        const bf16* dz; int dz_ctot, dz_c0, dz_c;
+        if (g.dlib_bn >= 0) { dz = T.dz.as<bf16>() + t.z_off; dz_ctot = g.cout; dz_c0 = 0; dz_c = g.cout; }
+        else if (g.out_level == -2) { dz = T.glogits16.as<bf16>(); dz_ctot = 8; dz_c0 = 0; dz_c = 8; }
+        else { dz = T.tg.level[ol].as<bf16>(); dz_ctot = plan_.level_channels[ol]; dz_c0 = g.out_c0; dz_c = g.cout; }
+
+        // filter gradient
+        tc::WgradJob& wj = t.wgrad;
+        wj = tc::WgradJob();
+        wj.dy = dz; wj.dy_ctot = dz_ctot; wj.dy_c0 = dz_c0; wj.cy = dz_c; wj.cy_real = g.cout;
+        wj.g = T.tw.geo[ol];
+        wj.out = G + g.w_off;
+        const int kk = g.ksize * g.ksize;
+        if (g.in_level < 0) { wj.x = T.tw.img.as<bf16>(); wj.x_ctot = 8; wj.x_c0 = 0; wj.cx = 8; }
+        else if (g.pool_input) { wj.x = T.tw.pool.as<bf16>() + T.tw.pool_off[gi]; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
+        else if (up) { wj.x = T.upx.as<bf16>() + t.upx_off; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
+        else { wj.x = T.tw.level[g.in_level].as<bf16>(); wj.x_ctot = plan_.level_channels[g.in_level]; wj.x_c0 = g.in_c0; wj.cx = g.cin; }
+        wj.cx_real = g.cin;
+        wj.ntaps = kk;
+        if (!g.is_cont) { wj.sy = (long long)g.cin * kk; wj.sx = kk; } else { wj.sy = kk; wj.sx = (long long)g.cout * kk; }
+        for (int ky = 0; ky < g.ksize; ++ky)
+            for (int kx = 0; kx < g.ksize; ++kx) {
+                const int i = ky * g.ksize + kx;
+                wj.tapmap[i] = i;
+                if (g.ksize == 1) { wj.tap_dy[i] = 0; wj.tap_dx[i] = 0; }
+                else if (!g.is_cont) { wj.tap_dy[i] = ky - 1; wj.tap_dx[i] = kx - 1; }   // dW[co][ci][ky][kx] = sum dz[p] x[p + (ky-1, kx-1)]
+                else if (!up) { wj.tap_dy[i] = 1 - ky; wj.tap_dx[i] = 1 - kx; }          // cont_ s1: x[p + (1-ky, 1-kx)]
+                else { wj.tap_dy[i] = -ky; wj.tap_dx[i] = -kx; }                         // cont_ s2: zero-stuffed x at p - (ky, kx)
+            }
+
+        // backward-data
+        if (g.in_level < 0) continue;
+        ConvSetup s;
+        s.src = dz; s.src_positions = T.tw.geo[ol].positions(); s.src_ctot = dz_ctot; s.a_c0 = dz_c0; s.cin = dz_c;
+        s.packed = T.bwd_packs.as<bf16>() + t.bwd_pack_off;
+        s.ntaps = t.bwd_ntaps;
+        for (int i = 0; i < s.ntaps; ++i) { s.tap_dy[i] = t.bwd_tapdy[i]; s.tap_dx[i] = t.bwd_tapdx[i]; }
+        s.npad_total = t.bwd_npad;
+        s.grid = T.tw.geo[ol];
+        t.dgrad.assign(1, ConvLaunch());
+        ConvLaunch& L = t.dgrad[0];
+        tc::setup_conv(L, s);
+        L.act = tc::ACT_NONE; L.bias = nullptr;
+        L.cout = g.cin;
+        if (g.pool_input) { L.mode = tc::OUT_BF16; L.out = T.dpool.as<bf16>() + t.dpool_off; L.out_ctot = g.cin; L.out_c0 = 0; }
+        else {
+            L.mode = up ? tc::OUT_BF16_DOWN_ACCUM : tc::OUT_BF16_ACCUM;
+            L.out = T.tg.level[g.in_level].p; L.out_ctot = plan_.level_channels[g.in_level]; L.out_c0 = g.in_c0;
+            if (up) { L.out_S = T.tw.geo[g.in_level].S(); L.out_P = T.tw.geo[g.in_level].P(); }
+        }
+        const double px = (double)s.grid.N * s.grid.H * s.grid.W;
+        L.flops = 2.0 * px * g.cin * g.cout * s.ntaps / (up ? 4.0 : 1.0);
+        L.bytes = 2.0 * px * (g.cin + g.cout);
+    }
+    tn_ = n; th_ = h; tw_ = w;
+    stats_valid_ = false;
+    T.train_ready = true;
+}
+
+void Engine::level_values(int level, bool gradient, std::vector<float>& out, int dims[4])
+{
+    if (tn_ == 0) throw state_error("no training step has run");
+    if (level < 0 || level > plan_.levels) throw std::invalid_argument("no such level");
+    synchronize();
+    const int C = plan_.level_channels[level];
+    if (precision_ == 1) {
+        TcState& T = *tc_;
+        const Geo& g = T.tw.geo[level];
+        dims[0] = g.N; dims[1] = C; dims[2] = g.H; dims[3] = g.W;
+        std::vector<uint16_t> raw((size_t)g.positions() * C);
+        AB_CUDA(cudaMemcpy(raw.data(), (gradient ? T.tg : T.tw).level[level].p, raw.size() * 2, cudaMemcpyDeviceToHost));
+        out.resize((size_t)g.N * C * g.H * g.W);
+        for (int n = 0; n < g.N; ++n)
+            for (int c = 0; c < C; ++c)
+                for (int y = 0; y < g.H; ++y)
+                    for (int x = 0; x < g.W; ++x) {
+                        const uint32_t bits = (uint32_t)raw[(size_t)g.pos(n, y, x) * C + c] << 16;
+                        float f;
+                        std::memcpy(&f, &bits, 4);
+                        out[(((size_t)n * C + c) * g.H + y) * g.W + x] = f;
+                    }
+    } else {
+        Levels& L = gradient ? tw_grad_ : tw_act_;
+        dims[0] = L.n; dims[1] = C; dims[2] = L.dims.h[level]; dims[3] = L.dims.w[level];
+        out.resize((size_t)dims[0] * dims[1] * dims[2] * dims[3]);
+        AB_CUDA(cudaMemcpy(out.data(), L.buf[level].p, out.size() * 4, cudaMemcpyDeviceToHost));
+    }
+}
+
+void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
+{
+    if (n < 2) throw std::invalid_argument("training needs a mini-batch of at least 2 (bn_ runs in batch mode only for num_samples > 1, layers.h:1392)");
+    tc_ensure_train(n, h, w);
+    TcState& T = *tc_;
+    const float* P = params_.as<float>();
+    float* G = grads_.as<float>();
+    const int K = plan_.class_count;
+
+    // bf16 filter packs of both directions from the fp32 master parameters
+    const tc::PackJob* jobs = T.pack_jobs.as<tc::PackJob>();
+    tc::pack_filters_batched(P, T.fwd_packs.as<bf16>(), jobs, T.n_fwd_jobs, T.max_pack_elems, stream_);
+    tc::pack_filters_batched(P, T.bwd_packs.as<bf16>(), jobs + T.n_fwd_jobs, T.n_pack_jobs - T.n_fwd_jobs, T.max_pack_elems, stream_);
+    T.fwd_packs_valid = true;
+
+    tc::image_to_nhwc(imgs_dev, h, w, 0, 0, T.tw.img.as<bf16>(), T.tw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+
+    // ---- forward (batch-norm training mode)
+    for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        TcGroup& t = T.groups[gi];
+        if (g.dead && hyper.skip_dead_layers) continue;
+        const int ol = g.out_level == -2 ? 0 : g.out_level;
+        const Geo& geo = T.tw.geo[ol];
+        if (g.pool_input)
+            tc::maxpool_nhwc(T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
+                             T.tw.pool.as<bf16>() + T.tw.pool_off[gi], geo, stream_);
+        for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, stream_);
+        if (g.dlib_bn >= 0) {
+            const int mish_first = g.bn_first ? 0 : 1;
+            float* stats = t_stats_.as<float>() + stats_off_[gi];
+            float* rmean = running_.as<float>() + running_off_[gi];
+            const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
+            tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_);
+            // layers.h:1392-1397: decay = 1 - num_updates/(num_updates+1); ++num_updates (capped by the window)
+            const double decay = 1.0 - (double)num_updates_[gi] / ((double)num_updates_[gi] + 1.0);
+            ++num_updates_[gi];
+            if (num_updates_[gi] > window_[gi]) num_updates_[gi] = window_[gi];
+            k::bn_finalize(T.sums.as<double>(), g.cout, (long long)n * geo.H * geo.W, (float)model_.layers[g.dlib_bn].eps, decay, rmean,
+                           rmean + g.cout, stats, stream_);
+            if (!g.dead) {
+                const View y{T.tw.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
+                tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_);
+            }
+        }
+    }
+    stats_valid_ = true;
+
+    // ---- loss + gradient at the logits (fp32 planes), then bf16 [positions][8] for the tensor-core backward
+    k::loss_forward_backward(t_logits_.as<float>(), labels_dev, t_glogits_.as<float>(), n, K, h, w, t_loss_.as<double>(), stream_);
+    tc::planes_to_nhwc8(t_glogits_.as<float>(), K, T.glogits16.as<bf16>(), T.tw.geo[0], stream_);
+
+    // ---- backward
+    for (int l = 0; l <= plan_.levels; ++l)
+        k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
+    const size_t np = plan_.num_params;
+    k::fill_zero(G, np * sizeof(float), stream_);
+    const int nbuckets = 4;
+    size_t bucket_hi = np;
+    for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
+        const ConvGroup& g = plan_.groups[gi];
+        TcGroup& t = T.groups[gi];
+        if (!g.dead) {
+            const int ol = g.out_level == -2 ? 0 : g.out_level;
+            const Geo& geo = T.tw.geo[ol];
+            const bool up = g.is_cont && g.stride == 2;
+            if (g.dlib_bn >= 0) {
+                const int mish_first = g.bn_first ? 0 : 1;
+                const float* stats = t_stats_.as<float>() + stats_off_[gi];
+                const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
+                const View dzv{T.dz.as<bf16>() + t.z_off, g.cout, 0, g.cout};
+                const View gy{T.tg.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
+                tc::bn_backward_reduce_nhwc(z, gy, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
+                                            stream_);
+                tc::bn_backward_apply_nhwc(z, gy, dzv, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
+                                           G + g.bn_off, G + g.bn_off + g.cout, G + g.b_off, stream_);
+            } else {
+                // bias gradient = channel sums of the gradient at the conv output (layers.h:226, cpu_dlib.cpp:470-504)
+                const tc::WgradJob& wj = t.wgrad;
+                const View dzv{const_cast<bf16*>(wj.dy), wj.dy_ctot, wj.dy_c0, wj.cy};
+                k::fill_zero(T.bias_tmp.p, sizeof(float) * 64, stream_);
+                tc::channel_sum_nhwc(dzv, geo, T.bias_tmp.as<float>(), stream_);
+                AB_CUDA(cudaMemcpyAsync(G + g.b_off, T.bias_tmp.p, sizeof(float) * g.cout, cudaMemcpyDeviceToDevice, stream_));
+            }
+            if (up) {
+                const View xin{T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<bf16>() + t.upx_off, geo, stream_);
+            }
+            tc::wgrad_mma(t.wgrad, T.wscratch.as<float>(), stream_);
+            for (const ConvLaunch& L : t.dgrad) tc::launch_conv(L, stream_);
+            if (g.pool_input) {
+                const View xin{T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                const View gin{T.tg.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                tc::maxpool_backward_nhwc(xin, T.tw.geo[g.in_level], T.dpool.as<bf16>() + t.dpool_off, geo, gin, stream_);
+            }
+        }
+        if (world_ > 1 && bucket_hi - g.w_off >= np / nbuckets) {
+            allreduce_range(g.w_off, bucket_hi);
+            bucket_hi = g.w_off;
+        }
+    }
+    if (world_ > 1) {
+        allreduce_range(0, bucket_hi);
+        AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
+        AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
+    }
+    if (update) optimizer_step();
+    AB_CUDA(cudaMemcpyAsync(loss_host_, t_loss_.p, sizeof(double), cudaMemcpyDeviceToHost, stream_));
+    AB_CUDA(cudaGetLastError());
+}
+
+}  // namespace ab

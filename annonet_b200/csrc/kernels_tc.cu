@@ -244,7 +244,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         const int half = (warp - 2) >> 2;    // which of every kEpiWarps/4 consecutive M tiles this warp takes
         constexpr int kTileStep = kEpiWarps / 4;
         const bool up = L.mode == OUT_BF16_UP || L.mode == OUT_BF16_UP_ACCUM;
-        const bool accum = L.mode == OUT_BF16_ACCUM || L.mode == OUT_BF16_UP_ACCUM;
+        const bool down = L.mode == OUT_BF16_DOWN_ACCUM;
+        const bool accum = L.mode == OUT_BF16_ACCUM || L.mode == OUT_BF16_UP_ACCUM || down;
         const int act = L.act, nblk = L.nblk, P = L.P, rows_per_sample = L.H + 1;
         // position step between this thread's consecutive tiles (kTileStep M tiles), as rows + columns of the [rows][P] array
         const int step_r = (kTileStep * L.m_pos_stride) / P, step_c = (kTileStep * L.m_pos_stride) % P;
@@ -278,6 +279,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                     // M grid = coarse tensor; row r <-> output rows 2r + a (r in [0, H] for a = 0, [0, H) for a = 1)
                     valid = valid && r <= L.H - L.par_a && c <= L.W - L.par_b;
                     opos = (long long)n * L.out_S + (long long)(2 * r + L.par_a + 1) * L.out_P + (2 * c + L.par_b + 1);
+                } else if (down) {
+                    // M grid = fine tensor; pixel (y, x) = (r - 1, c - 1) with y, x odd <-> coarse pixel ((y - 1)/2, (x - 1)/2)
+                    valid = valid && r >= 2 && c >= 2 && !((r | c) & 1) && r <= L.H - 1 && c <= L.W - 1;
+                    opos = (long long)n * L.out_S + (long long)(r >> 1) * L.out_P + (c >> 1);
                 } else {
                     valid = valid && r >= 1 && c >= 1;
                     opos = (long long)n * L.S + (long long)r * P + c;
@@ -318,7 +323,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                             }
                         }
                     }
-                    if (L.mode == OUT_F32_NCHW) {
+                    if (L.mode == OUT_F32_NHWC) {
+                        float4* o = reinterpret_cast<float4*>((float*)L.out + opos * L.out_ctot + L.out_c0 + co0);
+#pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4)
+                            if (co0 + 4 * i4 < L.cout) o[i4] = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                    } else if (L.mode == OUT_F32_NCHW) {
                         const long long hw = (long long)L.H * L.W;
                         float* o = (float*)L.out + ((long long)n * L.cout) * hw + (long long)(r - 1) * L.W + (c - 1);
 #pragma unroll

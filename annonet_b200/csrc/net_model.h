@@ -65,7 +65,8 @@ std::vector<Layer> static_layers(int levels, int class_count);
 // (layers.h:170-193,1340-1365): Glorot-uniform filters, zero biases, gamma 1, beta 0, running stats 0/1... .
 NetModel make_random_net(int class_count, double scaler, int min_filters, uint64_t seed, int levels = 6);
 
-NetModel parse_net(const void* bytes, size_t n, int levels = 6);
+// consumed == nullptr: the net must fill the buffer; else *consumed = bytes read (dlib streams are not length-prefixed)
+NetModel parse_net(const void* bytes, size_t n, int levels = 6, size_t* consumed = nullptr);
 std::vector<char> serialize_net(const NetModel& net);
 // RuntimeNet::operator=(TrainingNet): bn_ -> affine_ (layers.h:2144-2163)
 NetModel to_runtime(const NetModel& net);

@@ -130,7 +130,7 @@ static void write_details(Writer& w, const Layer& l)
     }
 }
 
-NetModel parse_net(const void* bytes, size_t nbytes, int levels)
+NetModel parse_net(const void* bytes, size_t nbytes, int levels, size_t* consumed)
 {
     NetModel net;
     net.levels = levels;
@@ -161,7 +161,8 @@ NetModel parse_net(const void* bytes, size_t nbytes, int levels)
         r.tensor(scratch);  // params_grad, or grad_final on the input-side layer
         if (i == n - 2) r.integer();  // sample_expansion_factor
     }
-    if (r.pos != nbytes) throw serialization_error(std::to_string(nbytes - r.pos) + " trailing bytes after the net");
+    if (consumed) *consumed = r.pos;
+    else if (r.pos != nbytes) throw serialization_error(std::to_string(nbytes - r.pos) + " trailing bytes after the net");
     if (saw_bn && saw_affine) throw serialization_error("stream mixes bn_con2 and affine_ records");
     net.is_training = !saw_affine;
     return net;

@@ -36,7 +36,10 @@ enum OutMode {
     OUT_BF16_ACCUM = 1,  // out[pos][c0 + co] += acc                        (gradient accumulation)
     OUT_F32_NCHW = 2,    // planes[n][co][y][x] = acc + bias                (class head -> logits)
     OUT_BF16_UP = 3,     // out[fine pos (2r + a, 2c + b)][c0 + co] = acc + bias   (cont_ stride 2, one parity class)
-    OUT_BF16_UP_ACCUM = 4
+    OUT_BF16_UP_ACCUM = 4,
+    OUT_F32_NHWC = 6,        // out32[pos][c0 + co] = acc + bias    (training: the fp32 conv output z that feeds a batch norm)
+    OUT_BF16_DOWN_ACCUM = 5  // out[coarse pos ((y-1)/2, (x-1)/2)][c0 + co] += acc at odd (y, x) of the fine M grid: backward-data of
+                             // the stride-2 cont_ (layers.h:542) evaluated as a stride-1 conv on the fine grid
 };
 enum Act { ACT_NONE = 0, ACT_MISH_AFFINE = 1, ACT_AFFINE_MISH = 2 };
 
@@ -112,6 +115,61 @@ void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* 
 // max_pool_<3,3,2,2,0,0> (cpu_dlib.cpp:1888-1943): channels [c0, c0 + C) of `in` (geometry gi, ctot channels) -> dense
 // pooled tensor [positions of go][C]
 void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st);
+
+// ---- training-side bf16 NHWC kernels (kernels_train_nhwc.cu) ------------------------------------
+// A "view" = channels [c0, c0 + C) of a padded flat tensor with ctot channels per position.
+struct View {
+    bf16* p = nullptr;
+    int ctot = 0, c0 = 0, C = 0;
+};
+struct ViewF {   // same, fp32 elements (the conv outputs z that feed a batch norm stay fp32: normalisation amplifies rounding)
+    float* p = nullptr;
+    int ctot = 0, c0 = 0, C = 0;
+};
+// sums[c] = sum x, sums[C + c] = sum x^2 over all positions of x = mish_first ? mish(z) : z (pads are zero and add nothing)
+void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st);
+// y = mish_first ? gamma*(mish(z)-mean)*invstd+beta : mish(gamma*(z-mean)*invstd+beta)   [mish optional]; pads are left alone
+void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, int has_mish, const float* gamma, const float* beta,
+                   const float* stats, cudaStream_t st);
+// backward pass 1 (cpu_dlib.cpp:1228-1250): red[c] = sum dv, red[C + c] = sum dv*xhat
+void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
+                             const float* beta, const float* stats, double* red, cudaStream_t st);
+// backward pass 2 (cpu_dlib.cpp:1252-1288): dz = gradient at the conv output (bf16, pads untouched), dgamma/dbeta from `red`,
+// dbias[c] = sum dz (assign_conv_bias_gradient, cpu_dlib.cpp:470-504; dbias must be zeroed by the caller)
+void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, const Geo& g, int mish_first, int has_mish, const float* gamma,
+                            const float* beta, const float* stats, const double* red, float* dgamma, float* dbeta, float* dbias,
+                            cudaStream_t st);
+// g[c] += sum over positions of v (caller zeroes g)
+void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st);
+// max_pool_<3,3,2,2,0,0> gradient (cpu_dlib.cpp:1971-2017): the first maximum of a window in row-major order receives it; gin +=
+void maxpool_backward_nhwc(const View& in, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
+// f32 planes [N][K][H][W] -> bf16 padded flat [positions][8] (channels >= K are zero)
+void planes_to_nhwc8(const float* planes, int K, bf16* out, const Geo& g, cudaStream_t st);
+// out (fine geometry, dense [positions][C]) = zero-stuffed in: out[2i][2j] = in[i][j], 0 at the other pixels
+void upsample_zero_nhwc(const View& in, const Geo& gc, bf16* out, const Geo& gf, cudaStream_t st);
+
+// one filter-pack job of pack_filters_batched: same element mapping as pack_filters_bf16
+struct PackJob {
+    long long w_off, packed_off;   // floats into the arena, bf16 elements into the pack buffer
+    long long sn, sk;
+    int nreal, npad, kreal, kp, ntaps;
+    int tapmap[9];
+};
+void pack_filters_batched(const float* arena, bf16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st);
+
+// ---- filter gradients on the tensor cores (kernels_wgrad_mma.cu) ----------------------------------
+//   G[tap][y][x] = sum_pos DY[pos][dy_c0 + y] * X[pos + tap_dy*P + tap_dx][x_c0 + x]      y < cy <= 64, x < cx
+// over ALL positions of geometry g (pads of both tensors are zero), scattered to out[y*sy + x*sx + tapmap[tap]].
+struct WgradJob {
+    const bf16* dy = nullptr; int dy_ctot = 0, dy_c0 = 0, cy = 0;   // cy, cx: loaded channels (multiples of 8)
+    const bf16* x = nullptr;  int x_ctot = 0, x_c0 = 0, cx = 0;
+    int cy_real = 0, cx_real = 0;                                    // channels written to `out` (<= cy, cx)
+    Geo g;
+    int ntaps = 0, tap_dy[9] = {0}, tap_dx[9] = {0}, tapmap[9] = {0};
+    float* out = nullptr; long long sy = 0, sx = 0;
+};
+size_t wgrad_mma_scratch_floats();
+void wgrad_mma(const WgradJob& job, float* scratch, cudaStream_t st);
 
 }  // namespace tc
 }  // namespace ab

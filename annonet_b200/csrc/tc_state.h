@@ -19,8 +19,12 @@ struct TcGroup {
     std::vector<tc::ConvLaunch> infer;   // prepared for the current inference geometry
     // training
     std::vector<tc::ConvLaunch> fwd;     // conv -> z (or destination)
-    size_t bwd_pack_off[4] = {0, 0, 0, 0};
+    size_t bwd_pack_off = 0;             // backward-data filters [tap][ci][co]
+    int bwd_npad = 0, bwd_ntaps = 0;
+    int bwd_tapmap[9] = {}, bwd_tapdy[9] = {}, bwd_tapdx[9] = {};
     std::vector<tc::ConvLaunch> dgrad;
+    tc::WgradJob wgrad;
+    size_t z_off = 0, dpool_off = 0, upx_off = 0;   // elements into TcState::z / dpool / upx
 };
 
 struct TcWorkspace {
@@ -39,8 +43,20 @@ struct TcState {
     TcWorkspace iw;            // inference
     // training
     TcWorkspace tw, tg;        // activations / gradients
-    DevBuf z, dz, dpool, glogits16, stats_sums;
-    std::vector<size_t> z_off;
+    DevBuf z;                  // per bn group: conv output z, fp32 [positions][cout]
+    DevBuf dz;                 // per bn group: gradient at the conv output, bf16 [positions][cout] (same element offsets as z)
+    DevBuf dpool;              // per transition_down group: gradient at the pooled tensor              [positions][cin]
+    DevBuf upx;                // per `up` group: zero-stuffed input on the fine grid (filter gradient)  [positions][cin]
+    DevBuf glogits16;          // loss gradient as bf16 [positions][8]
+    DevBuf sums, bias_tmp, wscratch, pack_jobs;
+    int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
+    bool train_ready = false;
 };
+
+// prepared launches of one conv group in the forward direction (engine_bf16.cu)
+void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const tc::bf16* packs,
+                            const float* P, std::vector<tc::ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0, int mode, int act);
+void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, cudaStream_t st);
+
 
 }  // namespace ab

@@ -93,6 +93,9 @@ ab_status ab_net_init_random(ab_net* net, int class_count, double width_scaler, 
 /* {Training,Runtime}Net::Deserialize (NetPimpl.cpp:170-198,305-320): a dlib stream of net_type
  * (bn_con2 records) or anet_type (affine_ records); which one is detected from the records. */
 ab_status ab_net_load_dlib(ab_net* net, const void* bytes, size_t n);
+/* Same for a buffer that continues after the net (dlib streams are not length-prefixed; deserialize(net, istream)
+ * leaves the stream right behind the net, dnn/core.h:2683-2692): *consumed = bytes of the net. */
+ab_status ab_net_load_dlib_prefix(ab_net* net, const void* bytes, size_t n, size_t* consumed);
 /* {Training,Runtime}Net::Serialize.  as_runtime=1 on a training net performs
  * RuntimeNet::operator=(TrainingNet) (NetPimpl.cpp:226-232): bn_ -> affine_ with the running
  * statistics folded in (layers.h:2144-2163).  *bytes is released with ab_free. */
@@ -156,6 +159,10 @@ ab_status ab_compute_gradients(ab_net* net, const uint8_t* images, const ab_wlab
                                double* loss);
 /* training-mode logits of the last step, NCHW f32 [n][class_count][h][w] */
 ab_status ab_get_logits(ab_net* net, float* out, size_t capacity_floats);
+/* every tensor living at one resolution level after the last training step -- the outputs (gradient = 0) or the
+ * gradient inputs (gradient = 1) dlib exposes as layer<i>(net).get_output() / get_gradient_input() (core.h:1021-1033) --
+ * as channel slices of one NCHW f32 block [n][level channels][h][w]; dims receives {n, c, h, w}; out may be NULL. */
+ab_status ab_get_level_tensor(ab_net* net, int level, int gradient, float* out, size_t capacity_floats, int32_t dims[4]);
 /* parameter gradients of one dlib layer<idx> in dlib's layout (visit_layer_parameter_gradients, core.h:3806-3816) */
 ab_status ab_get_layer_gradient(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
 ab_status ab_get_layer_params(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);

@@ -54,3 +54,70 @@ def test_bf16_tiled_inference_matches_fp32(ab, full_net):
     top2 = np.sort(b32, axis=0)[-2:]
     assert np.all((top2[1] - top2[0])[bad] < 2 * BF16_TOL * np.abs(b32).max())
     assert np.array_equal(l16, e16.infer(img, 256, 256))  # deterministic
+
+
+def _train_batch(ab, rng, n, h, w, k=3):
+    imgs = np.stack([synth_image(rng, h, w) for _ in range(n)])
+    labels = np.stack([synth_labels(rng, h, w, k) for _ in range(n)])
+    weights = np.stack([ab.set_weights(l, 0.5, 0.5) for l in labels])
+    return imgs, ab.pack_labels(labels, weights)
+
+
+def test_bf16_training_gradients_match_fp32_engine(ab, full_net):
+    """forward (batch-norm training mode) + loss + backward of the tensor-core path against the fp32 path, which the
+    parity tests pin to the reference: logits, loss and every layer's parameter gradient within the bf16 tolerance."""
+    rng = np.random.default_rng(19)
+    data = df.serialize_net(full_net)
+    imgs, wl = _train_batch(ab, rng, 6, 191, 255)
+    n32 = ab.TrainingNet(0, ab.AB_PRECISION_FP32)
+    n32.Deserialize(data)
+    n16 = ab.TrainingNet(0, ab.AB_PRECISION_BF16)
+    n16.Deserialize(data)
+    l32, l16 = n32.compute_gradients(imgs, wl), n16.compute_gradients(imgs, wl)
+    print(f"loss fp32 {l32:.6f} bf16 {l16:.6f}")
+    assert abs(l16 - l32) < BF16_TOL * abs(l32)
+    assert rel_err(n16.logits(), n32.logits()) < BF16_TOL
+    report = []
+    for i, layer in full_net.param_layers():
+        g32, g16 = n32.layer_gradient(i), n16.layer_gradient(i)
+        assert g32.shape == g16.shape
+        if np.abs(g32).max() == 0:
+            assert np.abs(g16).max() == 0, f"layer<{i}> is dead: its gradient must be exactly zero"
+            continue
+        # filters and bias (or gamma and beta) have very different magnitudes: judge each part against its own scale
+        nb = layer["num_filters"] if layer["type"] in ("con", "cont") else g32.size // 2
+        for part, sl in (("weights", slice(0, g32.size - nb)), ("bias", slice(g32.size - nb, g32.size))):
+            a, b = g16[sl], g32[sl]
+            if np.abs(b).max() < 1e-12:
+                continue
+            e = float(np.linalg.norm(a - b) / np.linalg.norm(b))
+            report.append((e, rel_err(a, b), i, part))
+    report.sort(reverse=True)
+    print("gradient errors, bf16 vs fp32 path (relative L2, max-norm relative, layer, part):")
+    for r in sorted(report, key=lambda r: -r[2]):
+        print("   %.3e  %.3e  layer<%d> %s" % r)
+    assert report[0][0] < BF16_TOL, f"layer<{report[0][2]}> {report[0][3]}: relative L2 error {report[0][0]:.3e}"
+
+
+def test_bf16_training_tracks_fp32(ab, full_net):
+    """a few SGD steps: the bf16 path's loss curve follows the fp32 path's, and the trained net converts to a runtime net."""
+    rng = np.random.default_rng(20)
+    data = df.serialize_net(full_net)
+    imgs, wl = _train_batch(ab, rng, 4, 127, 127)
+    curves = []
+    for prec in (ab.AB_PRECISION_FP32, ab.AB_PRECISION_BF16):
+        net = ab.TrainingNet(0, prec)
+        net.Deserialize(data)
+        net.SetLearningRate(0.05)
+        losses = []
+        for _ in range(6):
+            net.StartTraining(imgs, wl)
+            losses.append(net.sync())
+        curves.append(losses)
+        if prec == ab.AB_PRECISION_BF16:
+            rt = net.GetRuntimeNet(0, ab.AB_PRECISION_BF16)
+            assert np.isfinite(rt.Forward(imgs[0])).all()
+    print("loss fp32", ["%.4f" % v for v in curves[0]], "bf16", ["%.4f" % v for v in curves[1]])
+    assert curves[1][-1] < curves[1][0]
+    for a, b in zip(*curves):
+        assert abs(a - b) < 0.05 * abs(a)
