@@ -112,6 +112,7 @@ private:
     void tc_pack_forward_filters();
     void tc_ensure_train(int n, int h, int w);
     void tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
+    void tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
     std::unique_ptr<TcState> tc_;
 
     int device_, precision_;
@@ -123,7 +124,8 @@ private:
 
     DevBuf params_, grads_, mom_, adam_v_, lr_mul_, wd_mul_, running_;  // running_: per bn group [mean(C) | var(C)]
     std::vector<size_t> running_off_;   // per group
-    std::vector<unsigned long long> num_updates_, window_;  // per group
+    std::vector<unsigned long long> num_updates_, window_;  // per group; num_updates_ is a host mirror of nu_dev_ (load/snapshot)
+    DevBuf nu_dev_;                     // per group: bn_ num_updates counter, advanced on the device by bn_finalize
     unsigned long long adam_t_ = 0;
 
     // inference workspace

@@ -7,6 +7,7 @@
 //   update  : fp32 master parameters / fp32 gradient arena, the same fused SGD/Adam kernel as the fp32 path;
 //             the bf16 filter packs of both directions are rebuilt from the master copy by one batched kernel.
 #include "engine.h"
+#include "kcommon.cuh"
 #include "tc_state.h"
 
 #include <cstring>
@@ -66,6 +67,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
     if (K > 8) throw std::invalid_argument("the bf16 training path supports at most 8 classes in this build");
     ensure_workspace(T.tw, plan_, n, h, w, true, true, stream_);
     ensure_workspace(T.tg, plan_, n, h, w, false, false, stream_);
+    T.tw.pool_arg.reserve(std::max<size_t>(T.tw.pool.bytes / 2, 256));
     t_logits_.reserve((size_t)n * K * h * w * 4);
     t_glogits_.reserve((size_t)n * K * h * w * 4);
     t_loss_.reserve(sizeof(double));
@@ -255,10 +257,53 @@ void Engine::level_values(int level, bool gradient, std::vector<float>& out, int
     }
 }
 
+// One step = ~390 kernels, many of them a few microseconds long (the coarse levels): launch-bound when issued one by
+// one.  The step is static (shapes, pointers, the bn counters live on the device), so it is captured once into a CUDA
+// graph and replayed while nothing it bakes in changes (TcState::GraphKey).  Not captured: the first step of a
+// configuration (lazy module loading, cudaFuncSetAttribute), per-kernel profiling, Adam (its step counter is a kernel
+// argument) and data-parallel runs (NCCL runs on the side stream, eagerly).
 void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
 {
     if (n < 2) throw std::invalid_argument("training needs a mini-batch of at least 2 (bn_ runs in batch mode only for num_samples > 1, layers.h:1392)");
     tc_ensure_train(n, h, w);
+    TcState& T = *tc_;
+    static const bool no_graph = getenv("AB_NO_GRAPH") != nullptr;
+    if (no_graph || k::prof_enabled() || world_ > 1 || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update); return; }
+    TcState::GraphKey key;
+    key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
+    key.lr = hyper.learning_rate; key.wd = hyper.weight_decay; key.momentum = hyper.momentum; key.window = window_.empty() ? 0 : window_[0];
+    if (T.graph_exec && T.graph_key == key) {
+        AB_CUDA(cudaGraphLaunch(T.graph_exec, stream_));
+        k::count_launch((int)T.graph_kernels);
+        return;
+    }
+    if (!(T.seen_key == key)) {   // first time: run eagerly
+        T.seen_key = key;
+        tc_train_body(imgs_dev, labels_dev, n, h, w, update);
+        return;
+    }
+    if (T.graph_exec) { cudaGraphExecDestroy(T.graph_exec); T.graph_exec = nullptr; }
+    const unsigned long long k0 = k::g_launches.load();
+    cudaGraph_t graph = nullptr;
+    AB_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
+    try {
+        tc_train_body(imgs_dev, labels_dev, n, h, w, update);
+    } catch (...) {
+        cudaStreamEndCapture(stream_, &graph);
+        if (graph) cudaGraphDestroy(graph);
+        throw;
+    }
+    AB_CUDA(cudaStreamEndCapture(stream_, &graph));
+    T.graph_kernels = k::g_launches.load() - k0;
+    const cudaError_t e = cudaGraphInstantiate(&T.graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    AB_CUDA(e);
+    T.graph_key = key;
+    AB_CUDA(cudaGraphLaunch(T.graph_exec, stream_));
+}
+
+void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
+{
     TcState& T = *tc_;
     const float* P = params_.as<float>();
     float* G = grads_.as<float>();
@@ -281,7 +326,7 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
         const Geo& geo = T.tw.geo[ol];
         if (g.pool_input)
             tc::maxpool_nhwc(T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
-                             T.tw.pool.as<bf16>() + T.tw.pool_off[gi], geo, stream_);
+                             T.tw.pool.as<bf16>() + T.tw.pool_off[gi], geo, stream_, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi]);
         for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, stream_);
         if (g.dlib_bn >= 0) {
             const int mish_first = g.bn_first ? 0 : 1;
@@ -289,11 +334,7 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
             float* rmean = running_.as<float>() + running_off_[gi];
             const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
             tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_);
-            // layers.h:1392-1397: decay = 1 - num_updates/(num_updates+1); ++num_updates (capped by the window)
-            const double decay = 1.0 - (double)num_updates_[gi] / ((double)num_updates_[gi] + 1.0);
-            ++num_updates_[gi];
-            if (num_updates_[gi] > window_[gi]) num_updates_[gi] = window_[gi];
-            k::bn_finalize(T.sums.as<double>(), g.cout, (long long)n * geo.H * geo.W, (float)model_.layers[g.dlib_bn].eps, decay, rmean,
+            k::bn_finalize(T.sums.as<double>(), g.cout, (long long)n * geo.H * geo.W, (float)model_.layers[g.dlib_bn].eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean,
                            rmean + g.cout, stats, stream_);
             if (!g.dead) {
                 const View y{T.tw.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
@@ -346,9 +387,9 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
             tc::wgrad_mma(t.wgrad, T.wscratch.as<float>(), stream_);
             for (const ConvLaunch& L : t.dgrad) tc::launch_conv(L, stream_);
             if (g.pool_input) {
-                const View xin{T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
                 const View gin{T.tg.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
-                tc::maxpool_backward_nhwc(xin, T.tw.geo[g.in_level], T.dpool.as<bf16>() + t.dpool_off, geo, gin, stream_);
+                tc::maxpool_backward_nhwc(T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi], g.cin, T.tw.geo[g.in_level], T.dpool.as<bf16>() + t.dpool_off,
+                                          geo, gin, stream_);
             }
         }
         if (world_ > 1 && bucket_hi - g.w_off >= np / nbuckets) {

@@ -162,6 +162,8 @@ void Engine::load(const NetModel& m)
     AB_CUDA(cudaMemcpy(lr_mul_.p, lrm.data(), np * 4, cudaMemcpyHostToDevice));
     AB_CUDA(cudaMemcpy(wd_mul_.p, wdm.data(), np * 4, cudaMemcpyHostToDevice));
     if (roff) AB_CUDA(cudaMemcpy(running_.p, hr.data(), roff * 4, cudaMemcpyHostToDevice));
+    nu_dev_.reserve(sizeof(unsigned long long) * num_updates_.size());
+    AB_CUDA(cudaMemcpy(nu_dev_.p, num_updates_.data(), sizeof(unsigned long long) * num_updates_.size(), cudaMemcpyHostToDevice));
     AB_CUDA(cudaMemset(grads_.p, 0, np * 4));
     AB_CUDA(cudaMemset(mom_.p, 0, np * 4));
     if (adam_v_.p) AB_CUDA(cudaMemset(adam_v_.p, 0, np * 4));
@@ -180,6 +182,7 @@ NetModel Engine::snapshot(bool as_runtime)
     std::vector<float> hp(np), hr(running_.bytes / 4);
     AB_CUDA(cudaMemcpy(hp.data(), params_.p, np * 4, cudaMemcpyDeviceToHost));
     if (!hr.empty()) AB_CUDA(cudaMemcpy(hr.data(), running_.p, hr.size() * 4, cudaMemcpyDeviceToHost));
+    if (!num_updates_.empty()) AB_CUDA(cudaMemcpy(num_updates_.data(), nu_dev_.p, sizeof(unsigned long long) * num_updates_.size(), cudaMemcpyDeviceToHost));
     NetModel out = model_;
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
         const ConvGroup& g = plan_.groups[gi];

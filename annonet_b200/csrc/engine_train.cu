@@ -106,11 +106,7 @@ void Engine::forward_train(int n, int h, int w)
             float* stats = t_stats_.as<float>() + stats_off_[gi];
             float* rmean = running_.as<float>() + running_off_[gi];
             bn_stats(out, n, H, W, g.has_mish && mish_first, t_sums_.as<double>(), stream_);
-            // layers.h:1392-1397: decay = 1 - num_updates/(num_updates+1); ++num_updates (capped by the window)
-            const double decay = 1.0 - (double)num_updates_[gi] / ((double)num_updates_[gi] + 1.0);
-            ++num_updates_[gi];
-            if (num_updates_[gi] > window_[gi]) num_updates_[gi] = window_[gi];
-            bn_finalize(t_sums_.as<double>(), g.cout, (long long)n * hw, (float)model_.layers[g.dlib_bn].eps, decay, rmean, rmean + g.cout,
+            bn_finalize(t_sums_.as<double>(), g.cout, (long long)n * hw, (float)model_.layers[g.dlib_bn].eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean, rmean + g.cout,
                         stats, stream_);
             if (!g.dead)
                 bn_apply(out, y, n, H, W, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_);

@@ -70,8 +70,9 @@ void maxpool_backward(const Slice& in, const Slice& gout, const Slice& gin, int 
 void bn_stats(const Slice& z, int N, int H, int W, int mish_first, double* sums, cudaStream_t st);
 // mean/invstd (biased variance, eps), running stats with dlib's averaging factor (layers.h:1392-1397,
 // cpu_dlib.cpp:1127-1182); stats = [mean(C) | invstd(C)]
-void bn_finalize(const double* sums, int C, long long m, float eps, double decay, float* running_mean,
-                 float* running_var, float* stats, cudaStream_t st);
+// num_updates: device counter of this bn_ layer; decay = 1 - n/(n+1), then n = min(n+1, window)
+void bn_finalize(const double* sums, int C, long long m, float eps, unsigned long long* num_updates, unsigned long long window,
+                 float* running_mean, float* running_var, float* stats, cudaStream_t st);
 // y = mish_first ? gamma*(mish(z)-mean)*invstd+beta : mish(gamma*(z-mean)*invstd+beta)   [mish optional]
 void bn_apply(const Slice& z, const Slice& y, int N, int H, int W, int mish_first, int has_mish,
               const float* gamma, const float* beta, const float* stats, cudaStream_t st);

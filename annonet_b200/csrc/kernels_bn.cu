@@ -47,10 +47,17 @@ __global__ void __launch_bounds__(EW_T) bn_stats_kernel(const Slice z, const lon
     block_sum2_atomic((double)a, (double)b, sums + c, sums + z.C + c);
 }
 
-__global__ void bn_finalize_kernel(const double* __restrict__ sums, const int C, const double m, const double eps, const double decay,
+// one CTA; the counter is read by every thread before thread 0 advances it
+__global__ void bn_finalize_kernel(const double* __restrict__ sums, const int C, const double m, const double eps,
+                                   unsigned long long* __restrict__ num_updates, const unsigned long long window,
                                    float* __restrict__ rmean, float* __restrict__ rvar, float* __restrict__ stats)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = threadIdx.x;
+    const unsigned long long nu = *num_updates;
+    // layers.h:1392-1397: decay = 1 - num_updates/(num_updates+1); ++num_updates (capped by the window)
+    const double decay = 1.0 - (double)nu / ((double)nu + 1.0);
+    __syncthreads();
+    if (c == 0) *num_updates = nu + 1 > window ? window : nu + 1;
     if (c >= C) return;
     const float mean = (float)(sums[c] / m);
     const float sq = (float)(sums[C + c] / m);
@@ -215,10 +222,10 @@ void bn_stats(const Slice& z, int N, int H, int W, int mish_first, double* sums,
     count_launch();
 }
 
-void bn_finalize(const double* sums, int C, long long m, float eps, double decay, float* running_mean, float* running_var,
-                 float* stats, cudaStream_t st)
+void bn_finalize(const double* sums, int C, long long m, float eps, unsigned long long* num_updates, unsigned long long window,
+                 float* running_mean, float* running_var, float* stats, cudaStream_t st)
 {
-    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, C, (double)m, (double)eps, decay, running_mean, running_var, stats);
+    bn_finalize_kernel<<<1, (C + 31) / 32 * 32, 0, st>>>(sums, C, (double)m, (double)eps, num_updates, window, running_mean, running_var, stats);
     count_launch();
 }
 

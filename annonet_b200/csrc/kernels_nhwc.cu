@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) image_to_nhwc_kernel(const uint8_t* __res
 }
 
 __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const bf16* __restrict__ in, int in_ctot, int c0, int C8, int N, int Hi, int Wi,
-                                                           bf16* __restrict__ out, int Ho, int Wo)
+                                                           bf16* __restrict__ out, int Ho, int Wo, uint8_t* __restrict__ arg)
 {
     const long long total = (long long)N * Ho * Wo * C8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -56,8 +56,9 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const bf16* __restric
     const int n = (int)(p / Ho);
     const long long Si = (long long)(Hi + 1) * (Wi + 1), So = (long long)(Ho + 1) * (Wo + 1);
     float m[8];
+    uint32_t a[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) m[k] = -INFINITY;
+    for (int k = 0; k < 8; ++k) { m[k] = -INFINITY; a[k] = 0; }
 #pragma unroll
     for (int r = 0; r < 3; ++r)
 #pragma unroll
@@ -66,10 +67,17 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const bf16* __restric
             float f[8];
             unpack8(*reinterpret_cast<const BF8*>(in + pi * in_ctot + c0 + cg * 8), f);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) m[k] = fmaxf(m[k], f[k]);
+            for (int k = 0; k < 8; ++k)
+                if (f[k] > m[k]) { m[k] = f[k]; a[k] = r * 3 + q; }   // first maximum in row-major order (cpu_dlib.cpp:2003-2014)
         }
     const long long po = n * So + (long long)(y + 1) * (Wo + 1) + (x + 1);
     *reinterpret_cast<BF8*>(out + po * (C8 * 8) + cg * 8) = pack8(m);
+    if (arg) {   // training: which window element won, one byte per channel, for the gradient routing
+        uint2 w;
+        w.x = a[0] | (a[1] << 8) | (a[2] << 16) | (a[3] << 24);
+        w.y = a[4] | (a[5] << 8) | (a[6] << 16) | (a[7] << 24);
+        *reinterpret_cast<uint2*>(arg + po * (C8 * 8) + cg * 8) = w;
+    }
 }
 
 }  // namespace
@@ -83,11 +91,11 @@ void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* 
     k::count_launch();
 }
 
-void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st)
+void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st, uint8_t* arg)
 {
     const long long n = (long long)go.N * go.H * go.W * (C / 8);
     k::ProfScope ps(k::F_EW_BF16, 0, 2.0 * C * ((double)gi.N * gi.H * gi.W + (double)go.N * go.H * go.W), st);
-    maxpool_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, in_ctot, c0, C / 8, gi.N, gi.H, gi.W, out, go.H, go.W);
+    maxpool_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, in_ctot, c0, C / 8, gi.N, gi.H, gi.W, out, go.H, go.W, arg);
     k::count_launch();
 }
 

@@ -38,15 +38,44 @@ __device__ __forceinline__ void ldf8(const float* p, float f[8])
 }
 __device__ __forceinline__ void st8(bf16* p, const BF8& v) { *reinterpret_cast<BF8*>(p) = v; }
 
-struct GeoD { int N, H, W, P; long long S, total; };  // total = N * S
-GeoD geod(const Geo& g) { return GeoD{g.N, g.H, g.W, g.P(), g.S(), (long long)g.N * g.S()}; }
+struct GeoD { int N, H, W, P; unsigned S; long long total; };  // total = N * S  (< 2^31: checked by geod)
+GeoD geod(const Geo& g)
+{
+    if (g.positions() >= (1ll << 31)) throw std::invalid_argument("tensor too large for the bf16 NHWC kernels (positions must fit 31 bits)");
+    return GeoD{g.N, g.H, g.W, g.P(), (unsigned)g.S(), (long long)g.N * g.S()};
+}
 
-// is `pos` a real pixel (not a pad position)?
+// is `pos` a real pixel (not a pad position)?  32-bit arithmetic: positions fit 31 bits
 __device__ __forceinline__ bool is_pixel(const GeoD& g, long long pos)
 {
     if (pos >= g.total) return false;
-    const int rem = (int)(pos % g.S);
-    return rem >= g.P && (rem % g.P) != 0;
+    const unsigned rem = (unsigned)pos % g.S;
+    return rem >= (unsigned)g.P && (rem % (unsigned)g.P) != 0;
+}
+
+// mish_ (cpu_dlib.cpp:1510-1558) on the fast-math intrinsics: the results feed bf16 tensors or fp32 sums of bf16-rounded
+// data, so 2-ulp exp / division are far below the path's rounding noise.  e = inf -> r = 0 -> y = x.
+__device__ __forceinline__ float mish_fast(float x)
+{
+    const float e = __expf(x);
+    const float r = __fdividef(1.f, fmaf(e, e + 2.f, 2.f));
+    return fmaf(-2.f * x, r, x);
+}
+// y = mish(x), dy = mish'(x) from ONE exponential; dlib's clamps at |x| >= 8 (cpu_dlib.cpp:1531-1543)
+__device__ __forceinline__ void mish_both(float x, float& y, float& dy)
+{
+    const float e = __expf(x);
+    const float r = __fdividef(1.f, fmaf(e, e + 2.f, 2.f));
+    y = fmaf(-2.f * x, r, x);
+    const float omega = fmaf(4.f, x + 1.f, fmaf(e, fmaf(e, e + 4.f, fmaf(4.f, x, 6.f)), 0.f));
+    const float d = e * omega * r * r;
+    dy = x >= 8.f ? 1.f : (x <= -8.f ? 0.f : d);
+}
+__device__ __forceinline__ float mish_grad_fast(float x)
+{
+    float y, dy;
+    mish_both(x, y, dy);
+    return dy;
 }
 
 constexpr int kMaxT = 256;
@@ -81,7 +110,7 @@ __global__ void __launch_bounds__(kMaxT) bn_stats_kernel(const float* __restrict
         ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const float v = mish_first ? k::mish_f(f[i]) : f[i];
+            const float v = mish_first ? mish_fast(f[i]) : f[i];
             acc[0][i] += v;
             acc[1][i] = fmaf(v, v, acc[1][i]);
         }
@@ -109,9 +138,9 @@ __global__ void __launch_bounds__(kMaxT) bn_apply_kernel(const float* __restrict
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             float v = f[i];
-            if (has_mish && mish_first) v = k::mish_f(v);
+            if (has_mish && mish_first) v = mish_fast(v);
             v = fmaf(v - mean[i], sc[i], sh[i]);
-            if (has_mish && !mish_first) v = k::mish_f(v);
+            if (has_mish && !mish_first) v = mish_fast(v);
             f[i] = v;
         }
         st8(y + pos * y_ctot + y_c0 + c, pack8(f));
@@ -135,9 +164,9 @@ __global__ void __launch_bounds__(kMaxT) bn_bwd_reduce_kernel(const float* __res
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             float x = f[i], dv = d[i];
-            if (has_mish && mish_first) x = k::mish_f(x);
+            if (has_mish && mish_first) x = mish_fast(x);
             const float xhat = (x - mean[i]) * invstd[i];
-            if (has_mish && !mish_first) dv *= k::mish_grad_f(fmaf(xhat, ga[i], be[i]));
+            if (has_mish && !mish_first) dv *= mish_grad_fast(fmaf(xhat, ga[i], be[i]));
             acc[0][i] += dv;
             acc[1][i] = fmaf(dv, xhat, acc[1][i]);
         }
@@ -175,12 +204,12 @@ __global__ void __launch_bounds__(kMaxT) bn_bwd_apply_kernel(const float* __rest
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float zv = f[i];
-            float dv = d[i];
-            const float x = (has_mish && mish_first) ? k::mish_f(zv) : zv;
+            float dv = d[i], x = zv, dm = 1.f;
+            if (has_mish && mish_first) mish_both(zv, x, dm);
             const float xc = x - mean[i];
-            if (has_mish && !mish_first) dv *= k::mish_grad_f(fmaf(xc * invstd[i], ga[i], be[i]));
+            if (has_mish && !mish_first) dv *= mish_grad_fast(fmaf(xc * invstd[i], ga[i], be[i]));
             float r = fmaf(dv, k1[i], fmaf(k2[i], xc, k3[i]));
-            if (has_mish && mish_first) r *= k::mish_grad_f(zv);
+            if (has_mish && mish_first) r *= dm;
             f[i] = r;
             acc[0][i] += r;
         }
@@ -204,51 +233,42 @@ __global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const bf16* __restri
 }
 
 // gather form: an input pixel belongs to at most 2 x 2 windows and receives a window's gradient iff it is that window's
-// first maximum in row-major order
-__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const bf16* __restrict__ in, int in_ctot, int in_c0, int C8, int N, int Hi, int Wi,
+// first maximum in row-major order -- which element won is read from the byte map the forward pass wrote
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restrict__ arg, int C8, int N, int Hi, int Wi,
                                                           const bf16* __restrict__ gout, int Ho, int Wo, bf16* __restrict__ gin, int gin_ctot,
                                                           int gin_c0)
 {
     const long long total = (long long)N * Hi * Wi * C8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
-    const int cg = (int)(i % C8);
-    long long p = i / C8;
-    const int x = (int)(p % Wi); p /= Wi;
-    const int y = (int)(p % Hi);
-    const int n = (int)(p / Hi);
+    const int cg = (int)((unsigned long long)i % (unsigned)C8);
+    unsigned p = (unsigned)((unsigned long long)i / (unsigned)C8);
+    const int x = (int)(p % (unsigned)Wi); p /= (unsigned)Wi;
+    const int y = (int)(p % (unsigned)Hi);
+    const int n = (int)(p / (unsigned)Hi);
     const long long Si = (long long)(Hi + 1) * (Wi + 1), So = (long long)(Ho + 1) * (Wo + 1);
-    const int Pi = Wi + 1;
     float acc[8] = {};
     bool any = false;
-    for (int Y = max((y - 1) / 2, 0); Y <= min(y / 2, Ho - 1); ++Y) {
-        if (2 * Y > y || 2 * Y + 2 < y) continue;
-        for (int X = max((x - 1) / 2, 0); X <= min(x / 2, Wo - 1); ++X) {
-            if (2 * X > x || 2 * X + 2 < x) continue;
-            float m[8];
-            int arg[8];
+    const int Y0 = max((y - 1) >> 1, 0), Y1 = min(y >> 1, Ho - 1), X0 = max((x - 1) >> 1, 0), X1 = min(x >> 1, Wo - 1);
+    for (int Y = Y0; Y <= Y1; ++Y)
+        for (int X = X0; X <= X1; ++X) {
+            const long long po = (n * So + (long long)(Y + 1) * (Wo + 1) + (X + 1)) * (C8 * 8) + cg * 8;
+            const uint2 w = *reinterpret_cast<const uint2*>(arg + po);
+            const uint32_t mine = (uint32_t)((y - 2 * Y) * 3 + (x - 2 * X)) * 0x01010101u;
+            // bytes of w equal to `mine`: zero bytes of the xor
+            const uint32_t dx = w.x ^ mine, dy = w.y ^ mine;
+            if ((((dx - 0x01010101u) & ~dx) | ((dy - 0x01010101u) & ~dy)) & 0x80808080u) {
+                float go[8];
+                unpack8(ld8(gout + po), go);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { m[k] = -INFINITY; arg[k] = 0; }
-#pragma unroll
-            for (int r = 0; r < 3; ++r)
-#pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                    float f[8];
-                    unpack8(ld8(in + (n * Si + (long long)(2 * Y + r + 1) * Pi + (2 * X + q + 1)) * in_ctot + in_c0 + cg * 8), f);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        if (f[k] > m[k]) { m[k] = f[k]; arg[k] = r * 3 + q; }
+                for (int k = 0; k < 4; ++k) {
+                    if (((dx >> (8 * k)) & 0xffu) == 0) { acc[k] += go[k]; any = true; }
+                    if (((dy >> (8 * k)) & 0xffu) == 0) { acc[4 + k] += go[4 + k]; any = true; }
                 }
-            const int mine = (y - 2 * Y) * 3 + (x - 2 * X);
-            float go[8];
-            unpack8(ld8(gout + (n * So + (long long)(Y + 1) * (Wo + 1) + (X + 1)) * (C8 * 8) + cg * 8), go);
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-                if (arg[k] == mine) { acc[k] += go[k]; any = true; }
+            }
         }
-    }
     if (!any) return;
-    bf16* gp = gin + (n * Si + (long long)(y + 1) * Pi + (x + 1)) * gin_ctot + gin_c0 + cg * 8;
+    bf16* gp = gin + (n * Si + (long long)(y + 1) * (Wi + 1) + (x + 1)) * gin_ctot + gin_c0 + cg * 8;
     float old[8];
     unpack8(ld8(gp), old);
 #pragma unroll
@@ -372,12 +392,12 @@ void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st)
     k::count_launch();
 }
 
-void maxpool_backward_nhwc(const View& in, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st)
+void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st)
 {
-    const long long n = (long long)gi.N * gi.H * gi.W * (in.C / 8);
-    k::ProfScope ps(k::F_EW_BF16, 0, 2.0 * in.C * (3.0 * gi.N * gi.H * gi.W + (double)go.N * go.H * go.W), st);
-    maxpool_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in.p, in.ctot, in.c0, in.C / 8, gi.N, gi.H, gi.W, gout_dense, go.H, go.W,
-                                                                    gin.p, gin.ctot, gin.c0);
+    const long long n = (long long)gi.N * gi.H * gi.W * (C / 8);
+    if (n >= (1ll << 31) * 8) throw std::invalid_argument("maxpool_backward_nhwc: tensor too large");
+    k::ProfScope ps(k::F_EW_BF16, 0, 2.0 * C * (2.0 * gi.N * gi.H * gi.W + 1.5 * (double)go.N * go.H * go.W), st);
+    maxpool_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(arg, C / 8, gi.N, gi.H, gi.W, gout_dense, go.H, go.W, gin.p, gin.ctot, gin.c0);
     k::count_launch();
 }
 

@@ -114,7 +114,8 @@ void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* 
                    cudaStream_t st);
 // max_pool_<3,3,2,2,0,0> (cpu_dlib.cpp:1888-1943): channels [c0, c0 + C) of `in` (geometry gi, ctot channels) -> dense
 // pooled tensor [positions of go][C]
-void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st);
+// arg (optional, training): u8 [positions of go][C], the index (r*3 + q) of the window element that won
+void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st, uint8_t* arg = nullptr);
 
 // ---- training-side bf16 NHWC kernels (kernels_train_nhwc.cu) ------------------------------------
 // A "view" = channels [c0, c0 + C) of a padded flat tensor with ctot channels per position.
@@ -142,7 +143,8 @@ void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, cons
 // g[c] += sum over positions of v (caller zeroes g)
 void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st);
 // max_pool_<3,3,2,2,0,0> gradient (cpu_dlib.cpp:1971-2017): the first maximum of a window in row-major order receives it; gin +=
-void maxpool_backward_nhwc(const View& in, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
+// (`arg` as written by maxpool_nhwc in the forward pass)
+void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
 // f32 planes [N][K][H][W] -> bf16 padded flat [positions][8] (channels >= K are zero)
 void planes_to_nhwc8(const float* planes, int K, bf16* out, const Geo& g, cudaStream_t st);
 // out (fine geometry, dense [positions][C]) = zero-stuffed in: out[2i][2j] = in[i][j], 0 at the other pixels

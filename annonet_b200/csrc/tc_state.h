@@ -33,6 +33,7 @@ struct TcWorkspace {
     DevBuf level[8];           // bf16 [positions][level_channels]
     DevBuf img;                // bf16 [positions][8]
     DevBuf pool;               // pooled inputs of the transition_down groups, dense
+    DevBuf pool_arg;           // training: u8 index of the winning window element, same element offsets as `pool`
     std::vector<size_t> pool_off;  // per group, in elements
 };
 
@@ -51,6 +52,22 @@ struct TcState {
     DevBuf sums, bias_tmp, wscratch, pack_jobs;
     int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
     bool train_ready = false;
+    // CUDA graph of one whole training step (static shapes and pointers): replayed while the key stays the same
+    struct GraphKey {
+        const void* imgs = nullptr; const void* labels = nullptr;
+        int n = 0, h = 0, w = 0, update = 0, skip_dead = 0;
+        double lr = 0, wd = 0, momentum = 0;
+        unsigned long long window = 0;
+        bool operator==(const GraphKey& o) const
+        {
+            return imgs == o.imgs && labels == o.labels && n == o.n && h == o.h && w == o.w && update == o.update && skip_dead == o.skip_dead &&
+                   lr == o.lr && wd == o.wd && momentum == o.momentum && window == o.window;
+        }
+    };
+    GraphKey graph_key, seen_key;
+    cudaGraphExec_t graph_exec = nullptr;
+    unsigned long long graph_kernels = 0;   // kernels inside the graph (for ab_kernel_launches)
+    ~TcState() { if (graph_exec) cudaGraphExecDestroy(graph_exec); }
 };
 
 // prepared launches of one conv group in the forward direction (engine_bf16.cu)

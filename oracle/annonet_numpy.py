@@ -539,7 +539,7 @@ def _get_t(c, first_possible, first_in, last_in, last_possible):
 
 
 def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int, gains: Sequence[float] = (),
-                  overlap: Optional[int] = None, return_blended: bool = False, forward_fn=None):
+                  overlap: Optional[int] = None, return_blended: bool = False, forward_fn=None, rank: int = 0, world: int = 1):
     """annonet_infer(), annonet_infer.cpp:32-185 (without the detection-level blob filter):
     tiles -> enlarge to the recommended size around the centre -> clamp-to-edge fill (outpaint,
     annonet.h:74-120) -> Forward -> blend (double ramps, float accumulate) -> argmax."""
@@ -548,8 +548,14 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
     ov = overlap if overlap is not None else (1 << (levels + 1)) - 1
     tiles = get_tiles(w, h, max_tile_w, max_tile_h, ov, ov)
     blended = None
+    row, last_top = -1, None
     for tile in tiles:
         fl, ft, fr, fb = tile["full"]
+        # multi-GPU sharding of the engine: tile rows are dealt round-robin, canvases are summed afterwards
+        if ft != last_top:
+            row, last_top = row + 1, ft
+        if world > 1 and row % world != rank:
+            continue
         ul, ut, ur, ub = tile["unique"]
         fw, fh = fr - fl + 1, fb - ft + 1
         cx, cy = fl + fw // 2, ft + fh // 2
