@@ -198,6 +198,8 @@ void Engine::tc_ensure_train(int n, int h, int w)
                 else { wj.tap_dy[i] = -ky; wj.tap_dx[i] = -kx; }                         // cont_ s2: zero-stuffed x at p - (ky, kx)
             }
 
+        tc::setup_wgrad_tc(t.wgrad_tc, wj, T.wscratch.as<float>());
+
         // backward-data
         if (g.in_level < 0) continue;
         ConvSetup s;
@@ -384,7 +386,9 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
                 const View xin{T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
                 tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<bf16>() + t.upx_off, geo, stream_);
             }
-            tc::wgrad_mma(t.wgrad, T.wscratch.as<float>(), stream_);
+            static const bool wgrad_legacy = getenv("AB_WGRAD_MMA") != nullptr;   // warp-level mma.sync version, kept for A/B runs
+            if (wgrad_legacy) tc::wgrad_mma(t.wgrad, T.wscratch.as<float>(), stream_);
+            else tc::launch_wgrad_tc(t.wgrad_tc, stream_);
             for (const ConvLaunch& L : t.dgrad) tc::launch_conv(L, stream_);
             if (g.pool_input) {
                 const View gin{T.tg.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};

@@ -420,6 +420,11 @@ void make_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int
 
 }  // namespace
 
+void make_tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int box_ch, int box_rows)
+{
+    make_map_2d(m, base, rows, ctot, box_ch, box_rows, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+}
+
 int padded_n(int cout) { return (cout + 15) / 16 * 16; }
 int padded_k(int cin) { return (cin + 63) / 64 * 64; }
 

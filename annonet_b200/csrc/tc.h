@@ -170,8 +170,36 @@ struct WgradJob {
     int ntaps = 0, tap_dy[9] = {0}, tap_dx[9] = {0}, tapmap[9] = {0};
     float* out = nullptr; long long sy = 0, sx = 0;
 };
+// bf16 [rows][ctot] tensor, box {box_ch (16 / 32 / 64: 32 / 64 / 128-byte swizzle), box_rows}
+void make_tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int box_ch, int box_rows);
 size_t wgrad_mma_scratch_floats();
 void wgrad_mma(const WgradJob& job, float* scratch, cudaStream_t st);
+
+// The same GEMM on tcgen05 (kernels_wgrad_tc.cu): MN-major shared-memory descriptors over TMA-staged [position][64 channel]
+// tiles, two taps fused into one M = 128 MMA through the descriptor's leading-dimension offset, accumulators in TMEM.
+struct WgradTcLaunch {
+    alignas(64) CUtensorMap tmX, tmY;
+    int x_c0 = 0, dy_c0 = 0;
+    int th = 1, kw = 64;              // a chunk = th runs of kw positions; run m starts at o0 + m*run_stride
+    int run_stride = 0;
+    int rows_mode = 0, ncx = 1, P = 0;
+    int nseg = 1, seg_alloc = 0;      // X segments of a chunk (seg_alloc rows reserved each, multiple of 8)
+    int seg_pos[12] = {0};
+    int npairs = 0;                   // accumulators: tap pair (t1, t2) in rows 0-63 / 64-127
+    int pair_seg[5] = {0}, pair_off[5] = {0}, pair_lbo[5] = {0};   // segment (relative to the run) and row offset of t1; byte distance to t2
+    int pair_t1[5] = {0}, pair_t2[5] = {0};                          // tap ids (t2 = -1: none)
+    int N = 16;                       // padded cy
+    int stages = 2, tmem_cols = 64;
+    unsigned x_stage_bytes = 0, stage_bytes = 0, smem_bytes = 0;
+    long long chunks = 0;
+    int nsplit = 1, cxtiles = 1, ntaps = 0;
+    float* scratch = nullptr;
+    // reduction + scatter (same as WgradJob)
+    float* out = nullptr; long long sy = 0, sx = 0; int tapmap[9] = {0}; int cy_real = 0, cx_real = 0;
+    double flops = 0, bytes = 0;
+};
+void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch);
+void launch_wgrad_tc(const WgradTcLaunch& L, cudaStream_t st);
 
 }  // namespace tc
 }  // namespace ab

@@ -24,6 +24,7 @@ struct TcGroup {
     int bwd_tapmap[9] = {}, bwd_tapdy[9] = {}, bwd_tapdx[9] = {};
     std::vector<tc::ConvLaunch> dgrad;
     tc::WgradJob wgrad;
+    tc::WgradTcLaunch wgrad_tc;          // the same job prepared for the tcgen05 kernel
     size_t z_off = 0, dpool_off = 0, upx_off = 0;   // elements into TcState::z / dpool / upx
 };
 
