@@ -260,6 +260,17 @@ class RuntimeNet(_Net):
         _check(lib.ab_infer_tiled_device(self._h, C.c_void_p(image_ptr), h, w, max_tile_w, max_tile_h, None, 0, C.c_void_p(labels_ptr)))
 
 
+    def infer_partial_device(self, image_ptr: int, h: int, w: int, max_tile_w: int, max_tile_h: int, rank: int, world: int):
+        """this rank's tile rows blended into its private canvas; returns (device pointer, floats) of the canvas
+        for the caller's all-reduce."""
+        canvas, n = C.c_void_p(), C.c_size_t()
+        _check(lib.ab_infer_tiled_partial(self._h, C.c_void_p(image_ptr), h, w, max_tile_w, max_tile_h, rank, world, C.byref(canvas), C.byref(n)))
+        return canvas.value, n.value
+
+    def infer_finish_device(self, h: int, w: int, labels_ptr: int) -> None:
+        _check(lib.ab_infer_finish(self._h, h, w, None, 0, C.c_void_p(labels_ptr)))
+
+
 class TrainingNet(_Net):
     """NetPimpl::TrainingNet (NetPimpl.h:29-71)."""
 

@@ -10,6 +10,7 @@
 #include "kcommon.cuh"
 #include "tc_state.h"
 
+#include <cstdio>
 #include <cstring>
 
 namespace ab {
@@ -224,6 +225,39 @@ void Engine::tc_ensure_train(int n, int h, int w)
         L.flops = 2.0 * px * g.cin * g.cout * s.ntaps / (up ? 4.0 : 1.0);
         L.bytes = 2.0 * px * (g.cin + g.cout);
     }
+    // Gradient slices: the first writer of a channel range in backward order ASSIGNS (no read-modify-write on the epilogue's
+    // critical path, no memset of the level), later writers accumulate (dnn/core.h:958-974 zeroes x_grad and lets every
+    // consumer add; the static plan knows who comes first).  A level still needs zeroing when a writer would accumulate
+    // into channels nobody has assigned (max-pool gradient first, partial overlaps) or when channels are never written.
+    {
+        std::vector<std::vector<char>> written(plan_.levels + 1);
+        for (int l = 0; l <= plan_.levels; ++l) written[l].assign(plan_.level_channels[l], 0);
+        T.grad_level_needs_zero.assign(plan_.levels + 1, 0);
+        static const bool always_zero = getenv("AB_GRAD_MEMSET") != nullptr;
+        for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
+            const ConvGroup& g = plan_.groups[gi];
+            if (g.dead || g.in_level < 0) continue;
+            std::vector<char>& w = written[g.in_level];
+            int nw = 0;
+            for (int c = g.in_c0; c < g.in_c0 + g.cin; ++c) nw += w[c];
+            const bool none = nw == 0, all = nw == g.cin;
+            if (g.pool_input || always_zero) { if (!all) T.grad_level_needs_zero[g.in_level] = 1; }
+            else if (none) {
+                ConvLaunch& L = T.groups[gi].dgrad[0];
+                L.mode = L.mode == tc::OUT_BF16_DOWN_ACCUM ? tc::OUT_BF16_DOWN : tc::OUT_BF16;
+            } else if (!all) T.grad_level_needs_zero[g.in_level] = 1;
+            for (int c = g.in_c0; c < g.in_c0 + g.cin; ++c) w[c] = 1;
+        }
+        for (int l = 0; l <= plan_.levels; ++l)
+            for (char c : written[l])
+                if (!c) T.grad_level_needs_zero[l] = 1;
+        // one zeroing now: assigned slices keep their (never written) pad positions at zero from here on
+        for (int l = 0; l <= plan_.levels; ++l)
+            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
+        static const bool debug = getenv("AB_TC_DEBUG") != nullptr;
+        if (debug)
+            for (int l = 0; l <= plan_.levels; ++l) fprintf(stderr, "gradient level %d: memset per step %d\n", l, (int)T.grad_level_needs_zero[l]);
+    }
     tn_ = n; th_ = h; tw_ = w;
     stats_valid_ = false;
     T.train_ready = true;
@@ -270,7 +304,10 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
     tc_ensure_train(n, h, w);
     TcState& T = *tc_;
     static const bool no_graph = getenv("AB_NO_GRAPH") != nullptr;
-    if (no_graph || k::prof_enabled() || world_ > 1 || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update); return; }
+    // data parallel: the bucketed all-reduces fork to the communication stream and join back before the update, a
+    // pattern stream capture records as is (NCCL >= 2.9 supports capture); AB_NO_GRAPH_NCCL=1 keeps those runs eager
+    static const bool no_graph_nccl = getenv("AB_NO_GRAPH_NCCL") != nullptr;
+    if (no_graph || k::prof_enabled() || (world_ > 1 && no_graph_nccl) || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update); return; }
     TcState::GraphKey key;
     key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
     key.lr = hyper.learning_rate; key.wd = hyper.weight_decay; key.momentum = hyper.momentum; key.window = window_.empty() ? 0 : window_[0];
@@ -352,7 +389,8 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
 
     // ---- backward
     for (int l = 0; l <= plan_.levels; ++l)
-        k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
+        if (T.grad_level_needs_zero[l])
+            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
     const size_t np = plan_.num_params;
     k::fill_zero(G, np * sizeof(float), stream_);
     const int nbuckets = 4;

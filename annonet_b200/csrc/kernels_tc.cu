@@ -244,8 +244,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         const int half = (warp - 2) >> 2;    // which of every kEpiWarps/4 consecutive M tiles this warp takes
         constexpr int kTileStep = kEpiWarps / 4;
         const bool up = L.mode == OUT_BF16_UP || L.mode == OUT_BF16_UP_ACCUM;
-        const bool down = L.mode == OUT_BF16_DOWN_ACCUM;
-        const bool accum = L.mode == OUT_BF16_ACCUM || L.mode == OUT_BF16_UP_ACCUM || down;
+        const bool down = L.mode == OUT_BF16_DOWN_ACCUM || L.mode == OUT_BF16_DOWN;
+        const bool accum = L.mode == OUT_BF16_ACCUM || L.mode == OUT_BF16_UP_ACCUM || L.mode == OUT_BF16_DOWN_ACCUM;
         const int act = L.act, nblk = L.nblk, P = L.P, rows_per_sample = L.H + 1;
         // position step between this thread's consecutive tiles (kTileStep M tiles), as rows + columns of the [rows][P] array
         const int step_r = (kTileStep * L.m_pos_stride) / P, step_c = (kTileStep * L.m_pos_stride) % P;

@@ -79,6 +79,7 @@ __device__ __forceinline__ float mish_grad_fast(float x)
 }
 
 constexpr int kMaxT = 256;
+constexpr int kU = 2;   // positions per thread and loop iteration: their loads are issued together (memory-level parallelism)
 
 // sum the NV per-thread values over threadIdx.y and add them to out[v_base(k) + channel] with one atomic per value
 template <int NV, typename OutT>
@@ -100,120 +101,212 @@ __device__ __forceinline__ void block_reduce_channels(const float (&v)[NV][8], O
     }
 }
 
-__global__ void __launch_bounds__(kMaxT) bn_stats_kernel(const float* __restrict__ z, int ctot, int c0, long long npos, int mish_first,
-                                                         double* __restrict__ sums)
+// Per-channel constants live in SHARED memory (read back as float4 pairs), not in registers: the kernels below are
+// bound by memory latency, so what matters is how many threads with loads in flight fit on an SM (B200 needs ~45 KB in
+// flight per SM to saturate HBM).  Two positions per thread and iteration, loads issued before the first use.
+constexpr int kMaxC = 256;
+__device__ __forceinline__ void lds8(const float* p, float f[8])
+{
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+__global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restrict__ z, int ctot, int c0, long long npos, int mish_first,
+                                                            double* __restrict__ sums)
 {
     const int C8 = blockDim.x;
     float acc[2][8] = {};
-    for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < npos; pos += (long long)gridDim.x * blockDim.y) {
-        float f[8];
-        ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f);
+    const long long stride = (long long)gridDim.x * blockDim.y;
+    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < npos; p0 += kU * stride) {
+        float f[kU][8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float v = mish_first ? mish_fast(f[i]) : f[i];
-            acc[0][i] += v;
-            acc[1][i] = fmaf(v, v, acc[1][i]);
+        for (int u = 0; u < kU; ++u) {
+            const long long pos = p0 + u * stride;
+            if (pos < npos) ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f[u]);
+            else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[u][i] = 0.f;   // mish(0) = 0: adds nothing
+            }
         }
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float v = mish_first ? mish_fast(f[u][i]) : f[u][i];
+                acc[0][i] += v;
+                acc[1][i] = fmaf(v, v, acc[1][i]);
+            }
     }
     double* const dst[2] = {sums, sums + C8 * 8};
     block_reduce_channels<2, double>(acc, dst);
 }
 
-__global__ void __launch_bounds__(kMaxT) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, bf16* __restrict__ y, int y_ctot,
-                                                         int y_c0, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
-                                                         const float* __restrict__ beta, const float* __restrict__ stats)
+// y = mish_first ? mish(z)*sc + sh : mish(z*sc + sh),   sc = gamma*invstd, sh = beta - mean*sc
+__global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, bf16* __restrict__ y, int y_ctot,
+                                                            int y_c0, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, const float* __restrict__ stats)
 {
+    __shared__ __align__(16) float s_sc[kMaxC], s_sh[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
-    float mean[8], sc[8], sh[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        mean[i] = stats[c + i];
-        sc[i] = stats[C + c + i] * gamma[c + i];
-        sh[i] = beta[c + i];
+    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
+        const float sc = stats[C + i] * gamma[i];
+        s_sc[i] = sc;
+        s_sh[i] = beta[i] - stats[i] * sc;
     }
-    for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < g.total; pos += (long long)gridDim.x * blockDim.y) {
-        if (!is_pixel(g, pos)) continue;
-        float f[8];
-        ldf8(z + pos * z_ctot + z_c0 + c, f);
+    __syncthreads();
+    const long long stride = (long long)gridDim.x * blockDim.y;
+    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < g.total; p0 += kU * stride) {
+        float f[kU][8];
+        bool ok[kU];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float v = f[i];
-            if (has_mish && mish_first) v = mish_fast(v);
-            v = fmaf(v - mean[i], sc[i], sh[i]);
-            if (has_mish && !mish_first) v = mish_fast(v);
-            f[i] = v;
+        for (int u = 0; u < kU; ++u) {
+            const long long pos = p0 + u * stride;
+            ok[u] = is_pixel(g, pos);
+            if (ok[u]) ldf8(z + pos * z_ctot + z_c0 + c, f[u]);
         }
-        st8(y + pos * y_ctot + y_c0 + c, pack8(f));
+        float sc[8], sh[8];
+        lds8(s_sc + c, sc);
+        lds8(s_sh + c, sh);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            if (!ok[u]) continue;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float v = f[u][i];
+                if (has_mish && mish_first) v = mish_fast(v);
+                v = fmaf(v, sc[i], sh[i]);
+                if (has_mish && !mish_first) v = mish_fast(v);
+                f[u][i] = v;
+            }
+            st8(y + (p0 + u * stride) * y_ctot + y_c0 + c, pack8(f[u]));
+        }
     }
 }
 
-__global__ void __launch_bounds__(kMaxT) bn_bwd_reduce_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
-                                                              int gy_ctot, int gy_c0, long long npos, int mish_first, int has_mish,
-                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                              const float* __restrict__ stats, double* __restrict__ red)
+// xhat = x*I + M (I = invstd, M = -mean*invstd);  conv->bn->mish layers: dv *= mish'(xhat*gamma + beta)
+__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
+                                                                 int gy_ctot, int gy_c0, long long npos, int mish_first, int has_mish,
+                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                 const float* __restrict__ stats, double* __restrict__ red)
 {
+    __shared__ __align__(16) float s_i[kMaxC], s_m[kMaxC], s_g[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
-    float mean[8], invstd[8], ga[8], be[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { mean[i] = stats[c + i]; invstd[i] = stats[C + c + i]; ga[i] = gamma[c + i]; be[i] = beta[c + i]; }
+    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
+        s_i[i] = stats[C + i];
+        s_m[i] = -stats[i] * stats[C + i];
+        s_g[i] = gamma[i];
+        s_b[i] = beta[i];
+    }
+    __syncthreads();
+    const bool act_after = has_mish && !mish_first;
     float acc[2][8] = {};
-    for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < npos; pos += (long long)gridDim.x * blockDim.y) {
-        float f[8], d[8];
-        ldf8(z + pos * z_ctot + z_c0 + c, f);
-        unpack8(ld8(gy + pos * gy_ctot + gy_c0 + c), d);
+    const long long stride = (long long)gridDim.x * blockDim.y;
+    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < npos; p0 += kU * stride) {
+        float f[kU][8];
+        BF8 dq[kU];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float x = f[i], dv = d[i];
-            if (has_mish && mish_first) x = mish_fast(x);
-            const float xhat = (x - mean[i]) * invstd[i];
-            if (has_mish && !mish_first) dv *= mish_grad_fast(fmaf(xhat, ga[i], be[i]));
-            acc[0][i] += dv;
-            acc[1][i] = fmaf(dv, xhat, acc[1][i]);
+        for (int u = 0; u < kU; ++u) {
+            const long long pos = p0 + u * stride;
+            if (pos < npos) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
+            else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) dq[u].v[i] = __floats2bfloat162_rn(0.f, 0.f);   // dv = 0: adds nothing
+            }
+        }
+        float ci[8], cm[8];
+        lds8(s_i + c, ci);
+        lds8(s_m + c, cm);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            float d[8];
+            unpack8(dq[u], d);
+            if (act_after) {
+                float cg[8], cb[8];
+                lds8(s_g + c, cg);
+                lds8(s_b + c, cb);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) d[i] *= mish_grad_fast(fmaf(fmaf(f[u][i], ci[i], cm[i]), cg[i], cb[i]));
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float x = (has_mish && mish_first) ? mish_fast(f[u][i]) : f[u][i];
+                const float xhat = fmaf(x, ci[i], cm[i]);
+                acc[0][i] += d[i];
+                acc[1][i] = fmaf(d[i], xhat, acc[1][i]);
+            }
         }
     }
     double* const dst[2] = {red, red + C};
     block_reduce_channels<2, double>(acc, dst);
 }
 
-__global__ void __launch_bounds__(kMaxT) bn_bwd_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy, int gy_ctot,
-                                                             int gy_c0, bf16* __restrict__ dz, int dz_ctot, int dz_c0, GeoD g, int mish_first, int has_mish,
-                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                             const float* __restrict__ stats, const double* __restrict__ red, float invnum,
-                                                             float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias)
+// cpu_dlib.cpp:1228-1288 with the per-channel sums factored out (see kernels_bn.cu):
+//   dvars = -0.5*gamma*invstd^2 * sum(dv*xhat),  dmeans = -gamma*invstd * sum(dv)
+//   r = dv*k1 + k2*x + k3,   k1 = gamma*invstd,  k2 = 2*dvars/num,  k3 = dmeans/num - k2*mean
+// conv->mish->bn layers: x = mish(z), dz = r*mish'(z);   conv->bn->mish layers: x = z, dv *= mish'(x*A + B) first
+__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
+                                                                int gy_ctot, int gy_c0, bf16* __restrict__ dz, int dz_ctot, int dz_c0, GeoD g,
+                                                                int mish_first, int has_mish, const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, const float* __restrict__ stats,
+                                                                const double* __restrict__ red, float invnum, float* __restrict__ dgamma,
+                                                                float* __restrict__ dbeta, float* __restrict__ dbias)
 {
+    __shared__ __align__(16) float s_k1[kMaxC], s_k2[kMaxC], s_k3[kMaxC], s_a[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
-    float mean[8], invstd[8], ga[8], be[8], k1[8], k2[8], k3[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        mean[i] = stats[c + i]; invstd[i] = stats[C + c + i]; ga[i] = gamma[c + i]; be[i] = beta[c + i];
-        const float s_dv = (float)red[c + i], s_dvx = (float)red[C + c + i];
-        // cpu_dlib.cpp:1228-1288 with the per-channel sums factored out (see kernels_bn.cu)
-        const float dvars = -0.5f * ga[i] * invstd[i] * invstd[i] * s_dvx;
-        const float dmeans = -ga[i] * invstd[i] * s_dv;
-        k1[i] = ga[i] * invstd[i];
-        k2[i] = dvars * 2.f * invnum;
-        k3[i] = dmeans * invnum;
-        if (blockIdx.x == 0 && threadIdx.y == 0) { dgamma[c + i] = s_dvx; dbeta[c + i] = s_dv; }
+    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
+        const float mean = stats[i], invstd = stats[C + i], ga = gamma[i], be = beta[i];
+        const float s_dv = (float)red[i], s_dvx = (float)red[C + i];
+        const float dvars = -0.5f * ga * invstd * invstd * s_dvx, dmeans = -ga * invstd * s_dv;
+        const float k2 = dvars * 2.f * invnum;
+        s_k1[i] = ga * invstd;
+        s_k2[i] = k2;
+        s_k3[i] = dmeans * invnum - k2 * mean;
+        s_a[i] = invstd * ga;
+        s_b[i] = be - mean * invstd * ga;
+        if (blockIdx.x == 0) { dgamma[i] = s_dvx; dbeta[i] = s_dv; }
     }
+    __syncthreads();
+    const bool act_after = has_mish && !mish_first, act_before = has_mish && mish_first;
     float acc[1][8] = {};
-    for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < g.total; pos += (long long)gridDim.x * blockDim.y) {
-        if (!is_pixel(g, pos)) continue;
-        float f[8], d[8];
-        ldf8(z + pos * z_ctot + z_c0 + c, f);
-        unpack8(ld8(gy + pos * gy_ctot + gy_c0 + c), d);
+    const long long stride = (long long)gridDim.x * blockDim.y;
+    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < g.total; p0 += kU * stride) {
+        float f[kU][8];
+        BF8 dq[kU];
+        bool ok[kU];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float zv = f[i];
-            float dv = d[i], x = zv, dm = 1.f;
-            if (has_mish && mish_first) mish_both(zv, x, dm);
-            const float xc = x - mean[i];
-            if (has_mish && !mish_first) dv *= mish_grad_fast(fmaf(xc * invstd[i], ga[i], be[i]));
-            float r = fmaf(dv, k1[i], fmaf(k2[i], xc, k3[i]));
-            if (has_mish && mish_first) r *= dm;
-            f[i] = r;
-            acc[0][i] += r;
+        for (int u = 0; u < kU; ++u) {
+            const long long pos = p0 + u * stride;
+            ok[u] = is_pixel(g, pos);
+            if (ok[u]) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
         }
-        st8(dz + pos * dz_ctot + dz_c0 + c, pack8(f));
+        float k1[8], k2[8], k3[8];
+        lds8(s_k1 + c, k1);
+        lds8(s_k2 + c, k2);
+        lds8(s_k3 + c, k3);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            if (!ok[u]) continue;
+            float d[8];
+            unpack8(dq[u], d);
+            if (act_after) {
+                float ca[8], cb[8];
+                lds8(s_a + c, ca);
+                lds8(s_b + c, cb);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) d[i] *= mish_grad_fast(fmaf(f[u][i], ca[i], cb[i]));
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float x = f[u][i], dm = 1.f;
+                if (act_before) mish_both(f[u][i], x, dm);
+                const float r = fmaf(d[i], k1[i], fmaf(k2[i], x, k3[i])) * dm;
+                d[i] = r;
+                acc[0][i] += r;
+            }
+            st8(dz + (p0 + u * stride) * dz_ctot + dz_c0 + c, pack8(d));
+        }
     }
     float* const dst[1] = {dbias};
     block_reduce_channels<1, float>(acc, dst);

@@ -37,6 +37,7 @@ enum OutMode {
     OUT_F32_NCHW = 2,    // planes[n][co][y][x] = acc + bias                (class head -> logits)
     OUT_BF16_UP = 3,     // out[fine pos (2r + a, 2c + b)][c0 + co] = acc + bias   (cont_ stride 2, one parity class)
     OUT_BF16_UP_ACCUM = 4,
+    OUT_BF16_DOWN = 7,       // as OUT_BF16_DOWN_ACCUM, but assigns (first writer of the slice in a backward pass)
     OUT_F32_NHWC = 6,        // out32[pos][c0 + co] = acc + bias    (training: the fp32 conv output z that feeds a batch norm)
     OUT_BF16_DOWN_ACCUM = 5  // out[coarse pos ((y-1)/2, (x-1)/2)][c0 + co] += acc at odd (y, x) of the fine M grid: backward-data of
                              // the stride-2 cont_ (layers.h:542) evaluated as a stride-1 conv on the fine grid

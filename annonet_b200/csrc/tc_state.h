@@ -53,6 +53,7 @@ struct TcState {
     DevBuf sums, bias_tmp, wscratch, pack_jobs;
     int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
     bool train_ready = false;
+    std::vector<char> grad_level_needs_zero;   // per level: some writer accumulates into channels nobody assigned before it
     // CUDA graph of one whole training step (static shapes and pointers): replayed while the key stays the same
     struct GraphKey {
         const void* imgs = nullptr; const void* labels = nullptr;

@@ -55,7 +55,7 @@ class ClockSampler:
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -265,6 +265,14 @@ def own_arm(args):
     if rank == 0 and not args.no_infer:
         infer = bench_infer(ab, net, local, precision, torch)
 
+    # ---- secondary: tiled inference of a 16384 x 16384 image, 8 classes, tile rows sharded over the ranks (configs[2])
+    big = None
+    if not args.no_infer16k:
+        try:
+            big = bench_infer_sharded(ab, local, precision, torch, dist, rank, world)
+        except Exception as e:  # secondary figure: never lose the headline line over it
+            big = {"error": repr(e)[:300]}
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -310,7 +318,7 @@ def own_arm(args):
                 "d2h_bytes_per_step": 8, "timer": "host clock between device synchronizes, max over ranks"},
         "gpu_launches": int(launches),
         "roofline": roof, "kernel_families": families, "cpu_baseline": cpu,
-        "loss": {"after_warmup": loss0, "last": loss}, "inference": infer,
+        "loss": {"after_warmup": loss0, "last": loss}, "inference": infer, "inference_16k": big,
     }
     print(json.dumps(line))
     if world > 1:
@@ -350,6 +358,55 @@ def bench_infer(ab, train_net, device, precision, torch, reps=3):
             "tflops_algorithmic": FWD_FLOP_PER_PX * tile * tile / (ms * 1e-3) / 1e12}
 
 
+def bench_infer_sharded(ab, device, precision, torch, dist, rank, world, size=16384, tile=1024, classes=8, reps=2):
+    """BASELINE configs[2]: annonet_infer() of one size x size image, 8 classes; rank r runs the tile rows r, r + world, ...
+    into its private blend canvas, ONE all-reduce sums the canvases, every rank runs the argmax.
+    Device-resident image and label map; CUDA events on the engine's stream, max over ranks."""
+    import numpy as np
+    net = ab.TrainingNet(device, precision)
+    net.Initialize(classes, 1.0, 1, seed=2)
+    rt = net.GetRuntimeNet(device, precision)
+    del net
+    g = torch.Generator(device="cuda").manual_seed(7)
+    d_img = torch.randint(0, 256, (size, size, 3), dtype=torch.uint8, device="cuda", generator=g)
+    d_lab = torch.empty((size, size), dtype=torch.int16, device="cuda")
+    stream = torch.cuda.ExternalStream(rt.stream(), device=device)
+
+    def once():
+        ptr, n = rt.infer_partial_device(d_img.data_ptr(), size, size, tile, tile, rank, world)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                canvas = _as_tensor(torch, ptr, n, device)
+                dist.all_reduce(canvas)
+        rt.infer_finish_device(size, size, d_lab.data_ptr())
+
+    once()
+    rt.synchronize()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    e0.record(stream)
+    for _ in range(reps):
+        once()
+    e1.record(stream)
+    rt.synchronize()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    return {"workload": f"annonet_infer of one {size}x{size} RGB image, {classes} classes, tile {tile} (19 x 19 tiles), tile rows sharded over {world} GPU(s), "
+                        "one NCCL all-reduce of the blend canvas", "mpix_per_s": size * size / (ms * 1e-3) / 1e6, "ms": ms, "n_gpus": world}
+
+
+def _as_tensor(torch, ptr, n, device):
+    """a torch view of engine-owned device memory (the blend canvas) for torch.distributed's NCCL all-reduce"""
+    class _Cai:
+        __cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 3, "strides": None}
+    return torch.as_tensor(_Cai(), device=torch.device("cuda", device))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -360,6 +417,7 @@ def main():
                     help="bf16: tcgen05 tensor-core path (fp32 accumulate, fp32 master weights); fp32: FMA parity path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-infer", action="store_true", help="skip the secondary inference measurement")
+    ap.add_argument("--no-infer16k", action="store_true", help="skip the sharded 16384^2 tiled inference (BASELINE configs[2])")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
