@@ -304,9 +304,9 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
     tc_ensure_train(n, h, w);
     TcState& T = *tc_;
     static const bool no_graph = getenv("AB_NO_GRAPH") != nullptr;
-    // data parallel: the bucketed all-reduces fork to the communication stream and join back before the update, a
-    // pattern stream capture records as is (NCCL >= 2.9 supports capture); AB_NO_GRAPH_NCCL=1 keeps those runs eager
-    static const bool no_graph_nccl = getenv("AB_NO_GRAPH_NCCL") != nullptr;
+    // data parallel: steps run eagerly -- capturing the bucketed all-reduces (fork to the communication stream, join before
+    // the update) hung on the 2-GPU box with the torch-bundled NCCL 2.28; AB_GRAPH_NCCL=1 re-enables the attempt
+    static const bool no_graph_nccl = getenv("AB_GRAPH_NCCL") == nullptr;
     if (no_graph || k::prof_enabled() || (world_ > 1 && no_graph_nccl) || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update); return; }
     TcState::GraphKey key;
     key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
