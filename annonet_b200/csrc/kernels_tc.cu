@@ -520,7 +520,11 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
                 t_mma *= nchunks;
                 const double t_tma = 2.4 * nchunks * ((double)nseg * nloads * box_rows + (double)s.ntaps * L.nblk);
                 const double t_epi = 600.0 * th * (L.nblk / 16) * (rows_mode == 2 ? 1.15 : 1.0);
-                const double t_item = two ? std::max(std::max(t_mma, t_tma), t_epi) : std::max(t_tma, t_mma + t_epi);
+                // front end (TMA -> MMA) through `stages` shared-memory buffers: one buffer's cycle is fill + ~1 us of TMA / commit
+                // latency + consume, and `stages` of them overlap.  A single stage serialises all three (measured: the level-0
+                // data-gradient conv at kc 64 / 1 stage took 5.7k cycles per item against 2.4k modelled without this term).
+                const double t_front = std::max(std::max(t_tma, t_mma), (t_tma + t_mma + 1800.0 * nchunks) / stages);
+                const double t_item = two ? std::max(t_front, t_epi) : std::max(t_front, t_mma + t_epi);
                 const long long rounds = (ctas * nblocks + k::kNumSMs - 1) / k::kNumSMs;
                 (void)waste; (void)loadf;
                 double cost = (double)rounds * t_item + 3000.0;   // + pipeline fill / drain
