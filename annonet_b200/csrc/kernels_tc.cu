@@ -254,26 +254,35 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
             const int by = item / grid_x, bx = item - by * grid_x;
             const int n0 = by * nblk;
             // (sample, row, column) of this thread's first position; later tiles advance incrementally
-            int n, r, c, cx = 0;
-            if (L.rows_mode) {
-                const int rg = bx / L.ncx;
-                cx = bx - rg * L.ncx;
-                const int R = rg * L.th + half;            // global row of the [N*(H+1)][P] array
-                n = R / rows_per_sample; r = R - n * rows_per_sample;
-                c = cx * 128 + q * 32 + lane;
-            } else {
-                const int pos0 = bx * (128 * L.th) + half * 128 + q * 32 + lane;
-                n = pos0 / (int)L.S;
-                const int rem = pos0 - n * (int)L.S;
-                r = rem / P; c = rem - r * P;
-            }
-            const bool col_ok = c < P;
+            int n, r, c;
+            auto locate = [&](int m) {
+                if (L.rows_mode) {
+                    const int rg = bx / L.ncx, cx = bx - rg * L.ncx;
+                    const int R = rg * L.th + m;               // global row of the [N*(H+1)][P] array
+                    n = R / rows_per_sample; r = R - n * rows_per_sample;
+                    c = cx * 128 + q * 32 + lane;
+                } else {
+                    const int pos0 = bx * (128 * L.th) + m * 128 + q * 32 + lane;
+                    n = pos0 / (int)L.S;
+                    const int rem = pos0 - n * (int)L.S;
+                    r = rem / P; c = rem - r * P;
+                }
+            };
+            locate(half);
             const uint32_t buf = nbuf == 2 ? (ai & 1) : 0, use = ai / nbuf;
             mbar_wait(&acc_full[buf], use & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t tm = tmem + buf * (uint32_t)L.cols_buf + ((uint32_t)(q * 32) << 16);
-            for (int m = half; m < L.th; m += kTileStep) {
-                bool valid = n < L.Nsamples && col_ok;
+            // an odd tile count leaves one tile over: the two warp sets split its 16-channel blocks (even / odd)
+            const bool share = (L.th & 1) && nblk >= 32;
+            for (int m = half;; m += kTileStep) {
+                int jpar = -1;
+                if (m >= L.th) {
+                    if (!share || half == 0) break;
+                    m = L.th - 1; jpar = 1;
+                    locate(m);
+                } else if (share && m == L.th - 1) jpar = 0;
+                bool valid = n < L.Nsamples && c < P;
                 long long opos;
                 if (up) {
                     // M grid = coarse tensor; row r <-> output rows 2r + a (r in [0, H] for a = 0, [0, H) for a = 1)
@@ -287,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                     valid = valid && r >= 1 && c >= 1;
                     opos = (long long)n * L.S + (long long)r * P + c;
                 }
-                for (int j = 0; j < nblk; j += 16) {
+                for (int j = jpar > 0 ? 16 : 0; j < nblk; j += jpar >= 0 ? 32 : 16) {
                     float v[16];
                     if (NTAPS == 9 && L.kym) {
                         float w0[16], w1[16];
@@ -358,6 +367,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         }
                     }
                 }
+                if (jpar > 0) break;
                 // next tile of this thread
                 c += step_c; r += step_r;
                 if (c >= P) { c -= P; ++r; }
