@@ -373,11 +373,19 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             float* rmean = running_.as<float>() + running_off_[gi];
             const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
             tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_);
-            k::bn_finalize(T.sums.as<double>(), g.cout, (long long)n * geo.H * geo.W, (float)model_.layers[g.dlib_bn].eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean,
-                           rmean + g.cout, stats, stream_);
-            if (!g.dead) {
+            const double m = (double)((long long)n * geo.H * geo.W);
+            const float eps = (float)model_.layers[g.dlib_bn].eps;
+            if (g.dead) {
+                k::bn_finalize(T.sums.as<double>(), g.cout, (long long)m, eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean, rmean + g.cout, stats,
+                               stream_);
+            } else {
+                // bn_finalize folded into the apply kernel: one launch less per layer
+                tc::BnFinalize fin;
+                fin.sums = T.sums.as<double>(); fin.m = m; fin.eps = (double)eps;
+                fin.num_updates = nu_dev_.as<unsigned long long>() + gi; fin.window = window_[gi];
+                fin.rmean = rmean; fin.rvar = rmean + g.cout; fin.stats_out = stats;
                 const View y{T.tw.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
-                tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_);
+                tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_, &fin);
             }
         }
     }

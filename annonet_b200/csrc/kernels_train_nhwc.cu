@@ -144,14 +144,45 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
 // y = mish_first ? mish(z)*sc + sh : mish(z*sc + sh),   sc = gamma*invstd, sh = beta - mean*sc
 __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, bf16* __restrict__ y, int y_ctot,
                                                             int y_c0, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
-                                                            const float* __restrict__ beta, const float* __restrict__ stats)
+                                                            const float* __restrict__ beta, const float* __restrict__ stats,
+                                                            const BnFinalize fin)
 {
     __shared__ __align__(16) float s_sc[kMaxC], s_sh[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
-    for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
-        const float sc = stats[C + i] * gamma[i];
-        s_sc[i] = sc;
-        s_sh[i] = beta[i] - stats[i] * sc;
+    if (fin.sums) {
+        // same arithmetic as k::bn_finalize_kernel
+        const bool first = blockIdx.x == 0;
+        const unsigned long long nu = first ? *fin.num_updates : 0;
+        const double decay = 1.0 - (double)nu / ((double)nu + 1.0);
+        __syncthreads();   // every thread of CTA 0 has read the counter before it advances
+        if (first && threadIdx.x == 0 && threadIdx.y == 0) *fin.num_updates = nu + 1 > fin.window ? fin.window : nu + 1;
+        for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
+            const float mean = (float)(fin.sums[i] / fin.m);
+            const float sq = (float)(fin.sums[C + i] / fin.m);
+            const float var = sq - mean * mean;
+            const float invstd = (float)(1.0 / sqrt((double)var + fin.eps));
+            if (first) {
+                const double scale = fin.m / (fin.m - 1.0);  // unbiased running variance
+                if (decay == 1.0) {
+                    fin.rvar[i] = (float)(scale * var);
+                    fin.rmean[i] = mean;
+                } else {
+                    fin.rvar[i] = (float)((1 - decay) * fin.rvar[i] + scale * decay * var);
+                    fin.rmean[i] = (float)((1 - decay) * fin.rmean[i] + decay * mean);
+                }
+                fin.stats_out[i] = mean;
+                fin.stats_out[C + i] = invstd;
+            }
+            const float sc = invstd * gamma[i];
+            s_sc[i] = sc;
+            s_sh[i] = beta[i] - mean * sc;
+        }
+    } else {
+        for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
+            const float sc = stats[C + i] * gamma[i];
+            s_sc[i] = sc;
+            s_sh[i] = beta[i] - stats[i] * sc;
+        }
     }
     __syncthreads();
     const long long stride = (long long)gridDim.x * blockDim.y;
@@ -442,12 +473,12 @@ void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, c
 }
 
 void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, int has_mish, const float* gamma, const float* beta,
-                   const float* stats, cudaStream_t st)
+                   const float* stats, cudaStream_t st, const BnFinalize* fin)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total);
-    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats);
+    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{});
     k::count_launch();
 }
 

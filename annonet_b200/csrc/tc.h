@@ -131,8 +131,18 @@ struct ViewF {   // same, fp32 elements (the conv outputs z that feed a batch no
 // sums[c] = sum x, sums[C + c] = sum x^2 over all positions of x = mish_first ? mish(z) : z (pads are zero and add nothing)
 void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st);
 // y = mish_first ? gamma*(mish(z)-mean)*invstd+beta : mish(gamma*(z-mean)*invstd+beta)   [mish optional]; pads are left alone
+// Optional fused bn_finalize (kernels_bn.cu): every CTA derives mean / invstd from the layer's sums itself, CTA 0 also
+// updates the running statistics, the saved stats and the device-side num_updates counter (layers.h:1392-1397).
+struct BnFinalize {
+    const double* sums = nullptr;   // [2][C] sum, sum of squares (null: read `stats`)
+    double m = 0, eps = 0;
+    unsigned long long* num_updates = nullptr;
+    unsigned long long window = 0;
+    float* rmean = nullptr; float* rvar = nullptr;
+    float* stats_out = nullptr;     // [2][C] mean, invstd for the backward pass
+};
 void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, int has_mish, const float* gamma, const float* beta,
-                   const float* stats, cudaStream_t st);
+                   const float* stats, cudaStream_t st, const BnFinalize* fin = nullptr);
 // backward pass 1 (cpu_dlib.cpp:1228-1250): red[c] = sum dv, red[C + c] = sum dv*xhat
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
                              const float* beta, const float* stats, double* red, cudaStream_t st);
