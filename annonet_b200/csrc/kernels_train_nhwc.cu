@@ -121,8 +121,9 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
         float f[kU][8];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            const long long pos = p0 + u * stride;
-            if (pos < npos) ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f[u]);
+            // descending positions: the conv that produced z walked them upwards, so its last writes are still in L2
+            const long long pos = npos - 1 - (p0 + u * stride);
+            if (pos >= 0) ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f[u]);
             else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) f[u][i] = 0.f;   // mish(0) = 0: adds nothing
@@ -237,8 +238,9 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __
         BF8 dq[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            const long long pos = p0 + u * stride;
-            if (pos < npos) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
+            // descending positions: gy's producers and the apply pass that follows walk upwards (L2 reuse at both ends)
+            const long long pos = npos - 1 - (p0 + u * stride);
+            if (pos >= 0) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
             else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
