@@ -123,7 +123,7 @@ __device__ __forceinline__ float mish_fast(float x)
 // shared-memory stage ring (TMA -> MMA) and two TMEM accumulator buffers (MMA -> epilogue), so the TMA loads, the
 // tensor-core work and the epilogue of consecutive items overlap.
 template <int NTAPS>
-__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvLaunch L)
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvLaunch L, const int rev)
 {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], acc_full[2], acc_empty[2];
@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         if (elect_one()) {
             const uint32_t tx = (uint32_t)(L.nseg * L.seg_alloc + NTAPS * L.nblk) * pitch;
             uint32_t it = 0;
-            for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            for (int it0 = blockIdx.x; it0 < items; it0 += gridDim.x) {
+                const int item = rev ? items - 1 - it0 : it0;
                 const int by = item / grid_x, bx = item - by * grid_x;
                 const int n0 = by * L.nblk;
                 const int o0 = L.rows_mode ? (bx / L.ncx) * L.th * L.P + (bx % L.ncx) * 128 : bx * (128 * L.th);
@@ -250,7 +251,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         // position step between this thread's consecutive tiles (kTileStep M tiles), as rows + columns of the [rows][P] array
         const int step_r = (kTileStep * L.m_pos_stride) / P, step_c = (kTileStep * L.m_pos_stride) % P;
         uint32_t ai = 0;
-        for (int item = blockIdx.x; item < items; item += gridDim.x, ++ai) {
+        for (int it0 = blockIdx.x; it0 < items; it0 += gridDim.x, ++ai) {
+            const int item = rev ? items - 1 - it0 : it0;
             const int by = item / grid_x, bx = item - by * grid_x;
             const int n0 = by * nblk;
             // (sample, row, column) of this thread's first position; later tiles advance incrementally
@@ -576,7 +578,7 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
 }
 
 template <int NTAPS>
-static void launch_conv_t(const ConvLaunch& L, cudaStream_t st)
+static void launch_conv_t(const ConvLaunch& L, cudaStream_t st, int rev)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -584,17 +586,17 @@ static void launch_conv_t(const ConvLaunch& L, cudaStream_t st)
         attr_set = true;
     }
     const long long items = L.grid_x * (L.npad_total / L.nblk);
-    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::kNumSMs), kThreads, L.smem_bytes, st>>>(L);
+    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::kNumSMs), kThreads, L.smem_bytes, st>>>(L, rev);
 }
 
-void launch_conv(const ConvLaunch& L, cudaStream_t st)
+void launch_conv(const ConvLaunch& L, cudaStream_t st, int rev)
 {
     k::ProfScope ps(k::F_CONV_TC, L.flops, L.bytes, st);
     switch (L.ntaps) {
-    case 1: launch_conv_t<1>(L, st); break;
-    case 2: launch_conv_t<2>(L, st); break;
-    case 4: launch_conv_t<4>(L, st); break;
-    case 9: launch_conv_t<9>(L, st); break;
+    case 1: launch_conv_t<1>(L, st, rev); break;
+    case 2: launch_conv_t<2>(L, st, rev); break;
+    case 4: launch_conv_t<4>(L, st, rev); break;
+    case 9: launch_conv_t<9>(L, st, rev); break;
     default: throw std::logic_error("unsupported tap count");
     }
     k::count_launch();

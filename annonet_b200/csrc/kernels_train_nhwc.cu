@@ -112,7 +112,7 @@ __device__ __forceinline__ void lds8(const float* p, float f[8])
 }
 
 __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restrict__ z, int ctot, int c0, long long npos, int mish_first,
-                                                            double* __restrict__ sums)
+                                                            double* __restrict__ sums, int rev)
 {
     const int C8 = blockDim.x;
     float acc[2][8] = {};
@@ -121,9 +121,9 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
         float f[kU][8];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            // descending positions: the conv that produced z walked them upwards, so its last writes are still in L2
-            const long long pos = npos - 1 - (p0 + u * stride);
-            if (pos >= 0) ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f[u]);
+            // rev: descending positions -- a producer that walked upwards left its last writes in L2
+            const long long q = p0 + u * stride, pos = rev ? npos - 1 - q : q;
+            if (q < npos) ldf8(z + pos * ctot + c0 + threadIdx.x * 8, f[u]);
             else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) f[u][i] = 0.f;   // mish(0) = 0: adds nothing
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
 __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, bf16* __restrict__ y, int y_ctot,
                                                             int y_c0, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, const float* __restrict__ stats,
-                                                            const BnFinalize fin)
+                                                            const BnFinalize fin, int rev)
 {
     __shared__ __align__(16) float s_sc[kMaxC], s_sh[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
@@ -192,8 +192,8 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
         bool ok[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            const long long pos = p0 + u * stride;
-            ok[u] = is_pixel(g, pos);
+            const long long q = p0 + u * stride, pos = rev ? g.total - 1 - q : q;
+            ok[u] = q < g.total && is_pixel(g, pos);
             if (ok[u]) ldf8(z + pos * z_ctot + z_c0 + c, f[u]);
         }
         float sc[8], sh[8];
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
                 if (has_mish && !mish_first) v = mish_fast(v);
                 f[u][i] = v;
             }
-            st8(y + (p0 + u * stride) * y_ctot + y_c0 + c, pack8(f[u]));
+            st8(y + (rev ? g.total - 1 - (p0 + u * stride) : p0 + u * stride) * y_ctot + y_c0 + c, pack8(f[u]));
         }
     }
 }
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
 __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
                                                                  int gy_ctot, int gy_c0, long long npos, int mish_first, int has_mish,
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                 const float* __restrict__ stats, double* __restrict__ red)
+                                                                 const float* __restrict__ stats, double* __restrict__ red, int rev)
 {
     __shared__ __align__(16) float s_i[kMaxC], s_m[kMaxC], s_g[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
@@ -238,9 +238,8 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __
         BF8 dq[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            // descending positions: gy's producers and the apply pass that follows walk upwards (L2 reuse at both ends)
-            const long long pos = npos - 1 - (p0 + u * stride);
-            if (pos >= 0) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
+            const long long q = p0 + u * stride, pos = rev ? npos - 1 - q : q;
+            if (q < npos) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
             else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
@@ -284,7 +283,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
                                                                 int mish_first, int has_mish, const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, const float* __restrict__ stats,
                                                                 const double* __restrict__ red, float invnum, float* __restrict__ dgamma,
-                                                                float* __restrict__ dbeta, float* __restrict__ dbias)
+                                                                float* __restrict__ dbeta, float* __restrict__ dbias, int rev)
 {
     __shared__ __align__(16) float s_k1[kMaxC], s_k2[kMaxC], s_k3[kMaxC], s_a[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
@@ -310,8 +309,8 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
         bool ok[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
-            const long long pos = p0 + u * stride;
-            ok[u] = is_pixel(g, pos);
+            const long long q = p0 + u * stride, pos = rev ? g.total - 1 - q : q;
+            ok[u] = q < g.total && is_pixel(g, pos);
             if (ok[u]) { ldf8(z + pos * z_ctot + z_c0 + c, f[u]); dq[u] = ld8(gy + pos * gy_ctot + gy_c0 + c); }
         }
         float k1[8], k2[8], k3[8];
@@ -338,7 +337,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
                 d[i] = r;
                 acc[0][i] += r;
             }
-            st8(dz + (p0 + u * stride) * dz_ctot + dz_c0 + c, pack8(d));
+            st8(dz + (rev ? g.total - 1 - (p0 + u * stride) : p0 + u * stride) * dz_ctot + dz_c0 + c, pack8(d));
         }
     }
     float* const dst[1] = {dbias};
@@ -464,48 +463,48 @@ Shape channel_shape(int C, long long npos)
 
 }  // namespace
 
-void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st)
+void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 3.0 * g.N * g.H * g.W * z.C, 2.0 * g.N * g.H * g.W * z.C, st);
     cudaMemsetAsync(sums, 0, sizeof(double) * 2 * z.C, st);
     const Shape s = channel_shape(z.C, d.total);
-    bn_stats_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, d.total, mish_first, sums);
+    bn_stats_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, d.total, mish_first, sums, rev);
     k::count_launch();
 }
 
 void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, int has_mish, const float* gamma, const float* beta,
-                   const float* stats, cudaStream_t st, const BnFinalize* fin)
+                   const float* stats, cudaStream_t st, const BnFinalize* fin, int rev)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total);
-    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{});
+    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
     k::count_launch();
 }
 
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
-                             const float* beta, const float* stats, double* red, cudaStream_t st)
+                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 6.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
     cudaMemsetAsync(red, 0, sizeof(double) * 2 * z.C, st);
     const Shape s = channel_shape(z.C, d.total);
     bn_bwd_reduce_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, d.total, mish_first, has_mish, gamma, beta, stats,
-                                                     red);
+                                                     red, rev);
     k::count_launch();
 }
 
 void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, const Geo& g, int mish_first, int has_mish, const float* gamma,
                             const float* beta, const float* stats, const double* red, float* dgamma, float* dbeta, float* dbias,
-                            cudaStream_t st)
+                            cudaStream_t st, int rev)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 8.0 * g.N * g.H * g.W * z.C, 6.0 * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total);
     const float invnum = 1.0f / (float)((long long)g.N * g.H * g.W);
     bn_bwd_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, dz.p, dz.ctot, dz.c0, d, mish_first, has_mish, gamma, beta, stats, red,
-                                                    invnum, dgamma, dbeta, dbias);
+                                                    invnum, dgamma, dbeta, dbias, rev);
     k::count_launch();
 }
 

@@ -66,17 +66,17 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar)
 {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate)
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t b_hi, uint32_t idesc, uint32_t accumulate)
 {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         ".reg .b64 da, db;\n"
-        "setp.ne.b32 p, %5, 0;\n"
+        "setp.ne.b32 p, %6, 0;\n"
         "mov.b64 da, {%1, %3};\n"
-        "mov.b64 db, {%2, %3};\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
-        "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+        "mov.b64 db, {%2, %4};\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float v[16])
 {
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
 
     if (warp == 0) {
         if (elect_one()) {
-            const uint32_t tx = L.stage_bytes;
+            const uint32_t tx = L.x_stage_bytes + (uint32_t)(L.th * L.kw) * (L.shift ? 96u : 128u);
             uint32_t it = 0;
             for (long long chunk = c_begin; chunk < c_end; ++chunk, ++it) {
                 const int s = it % L.stages;
@@ -130,16 +130,22 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 const uint32_t xs = smem0 + (uint32_t)s * L.stage_bytes, ys = xs + L.x_stage_bytes;
                 for (int sg = 0; sg < L.nseg; ++sg)
                     tma_2d(xs + (uint32_t)(sg * L.seg_alloc) * 128u, &L.tmX, L.x_c0 + cxt * 64, o0 + L.seg_pos[sg], &full_bar[s]);
-                for (int m = 0; m < L.th; ++m)
-                    tma_2d(ys + (uint32_t)(m * L.kw) * 128u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
+                for (int m = 0; m < L.th; ++m) {
+                    if (L.shift) {
+                        for (int sft = 0; sft < 3; ++sft)
+                            tma_2d(ys + (uint32_t)((m * 3 + sft) * L.kw) * 32u, &L.tmY, L.dy_c0, o0 + m * L.run_stride + sft, &full_bar[s]);
+                    } else tma_2d(ys + (uint32_t)(m * L.kw) * 128u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
+                }
             }
         }
     } else if (warp == 1) {
         if (elect_one()) {
             // instruction descriptor: D f32, A/B bf16, both MN-major (bits 15, 16), N, M = 128
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(L.N >> 3) << 17) | ((128u >> 4) << 24);
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(L.Nmma >> 3) << 17) | ((128u >> 4) << 24);
             // descriptor high word: SBO = 1024 bytes (8 positions), version 1, 128-byte swizzle
             const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            // B in shift mode: SBO = 256 bytes (8 positions of 32 bytes), 32-byte swizzle
+            const uint32_t b_hi = L.shift ? (256u >> 4) | (1u << 14) | (6u << 29) : desc_hi;
             const int ksteps = L.kw / 16, npairs = L.npairs;
             uint32_t pa_off[5], pa_lbo[5];
             for (int a = 0; a < 5; ++a) {
@@ -154,12 +160,14 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 const uint32_t xs16 = (smem0 + (uint32_t)s * L.stage_bytes) >> 4, ys16 = xs16 + (L.x_stage_bytes >> 4);
                 for (int m = 0; m < L.th; ++m)
                     for (int kk = 0; kk < ksteps; ++kk) {
-                        const uint32_t b_lo = (ys16 + (uint32_t)(m * L.kw + kk * 16) * 8u) | (1u << 16);
+                        // shift mode: three 16-channel atoms (one per shift), LBO = one [kw][16] sub-tile apart, 32-byte rows
+                        const uint32_t b_lo = L.shift ? (ys16 + (uint32_t)(m * 3 * L.kw + kk * 16) * 2u) | ((uint32_t)(L.kw * 2) << 16)
+                                                      : (ys16 + (uint32_t)(m * L.kw + kk * 16) * 8u) | (1u << 16);
                         const uint32_t a_base = xs16 + (uint32_t)(m * L.seg_alloc + kk * 16) * 8u;
                         const uint32_t acc = (uint32_t)(it | m | kk);
 #pragma unroll
                         for (int a = 0; a < 5; ++a)
-                            if (a < npairs) umma_bf16(tmem + (uint32_t)(a * L.N), (a_base + pa_off[a]) | pa_lbo[a], b_lo, desc_hi, idesc, acc);
+                            if (a < npairs) umma_bf16(tmem + (uint32_t)(a * L.Nmma), (a_base + pa_off[a]) | pa_lbo[a], b_lo, desc_hi, b_hi, idesc, acc);
                     }
                 umma_commit(&empty_bar[s]);
             }
@@ -174,11 +182,13 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
         float* sc = L.scratch + ((size_t)split * L.cxtiles + cxt) * L.ntaps * 4096;
         for (int a = 0; a < L.npairs; ++a) {
             const int tap = q < 2 ? L.pair_t1[a] : L.pair_t2[a];
-            for (int j = 0; j < L.N; j += 16) {
+            for (int j = 0; j < L.Nmma; j += 16) {
                 float v[16];
-                tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * L.N + j), v);
-                if (tap >= 0) {
-                    float* o = sc + (size_t)tap * 4096 + (size_t)j * 64 + x;
+                tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * L.Nmma + j), v);
+                // shift mode: column block j / 16 is the dx tap of this row half's dy; else 16 more DY channels of `tap`
+                const int tp = L.shift ? L.sh_tap[a][q >> 1][j >> 4] : tap;
+                if (tp >= 0) {
+                    float* o = sc + (size_t)tp * 4096 + (size_t)(L.shift ? 0 : j) * 64 + x;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) o[i * 64] = v[i];
                 }
@@ -238,11 +248,26 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     L.x_c0 = job.x_c0; L.dy_c0 = job.dy_c0;
     L.ntaps = job.ntaps;
     L.N = padded_n(job.cy);
+    for (int t = 0; t < job.ntaps; ++t) L.tapmap[t] = job.tapmap[t];
+    // shift mode: a full 3x3 stencil with at most 16 output channels; the A side then sees three taps (dy, +1) only
+    static const bool no_shift = getenv("AB_WGRAD_NOSHIFT") != nullptr;
+    int grid3[3][3];
+    for (auto& r : grid3) for (int& v : r) v = -1;
+    bool full3 = job.ntaps == 9 && L.N == 16 && !no_shift;
+    for (int t = 0; t < job.ntaps && full3; ++t) {
+        if (std::abs(job.tap_dy[t]) > 1 || std::abs(job.tap_dx[t]) > 1 || grid3[job.tap_dy[t] + 1][job.tap_dx[t] + 1] >= 0) full3 = false;
+        else grid3[job.tap_dy[t] + 1][job.tap_dx[t] + 1] = t;
+    }
+    int ntaps = job.ntaps, tdy[9], tdx[9];
+    for (int t = 0; t < job.ntaps; ++t) { tdy[t] = job.tap_dy[t]; tdx[t] = job.tap_dx[t]; }
+    if (full3) {
+        ntaps = 3;
+        for (int t = 0; t < 3; ++t) { tdy[t] = t - 1; tdx[t] = 1; }
+    }
     int dylo = 0, dyhi = 0, dxlo = 0, dxhi = 0;
-    for (int t = 0; t < job.ntaps; ++t) {
-        dylo = std::min(dylo, job.tap_dy[t]); dyhi = std::max(dyhi, job.tap_dy[t]);
-        dxlo = std::min(dxlo, job.tap_dx[t]); dxhi = std::max(dxhi, job.tap_dx[t]);
-        L.tapmap[t] = job.tapmap[t];
+    for (int t = 0; t < ntaps; ++t) {
+        dylo = std::min(dylo, tdy[t]); dyhi = std::max(dyhi, tdy[t]);
+        dxlo = std::min(dxlo, tdx[t]); dxhi = std::max(dxhi, tdx[t]);
     }
     const int dyr = dyhi - dylo, dxr = dxhi - dxlo;
     // chunk geometry: runs of kw positions.  When kw divides the row pitch, `th` consecutive image rows share their halo
@@ -253,7 +278,7 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     double best = 1e300;
     auto consider = [&](int rows_mode, int kw, int th) {
         const int nseg = th + dyr, seg_alloc = (kw + dxr + 7) / 8 * 8;
-        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = xb + (size_t)th * kw * 128;
+        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = (xb + (size_t)th * kw * (full3 ? 96 : 128) + 1023) / 1024 * 1024;
         if (nseg > 12 || seg_alloc > 256 || 2 * sb + 1024 > budget) return;
         const int stages = (int)std::min<size_t>(kWMaxStages, (budget - 1024) / sb);
         const double score = (double)(nseg * seg_alloc + th * kw) / (th * kw) * (stages >= 3 ? 1.0 : 1.15);
@@ -279,18 +304,26 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     } else L.chunks = (total + L.kw - 1) / L.kw;
     // taps sorted by their address inside the staged segments, then paired
     int order[9], key[9];
-    for (int t = 0; t < job.ntaps; ++t) { order[t] = t; key[t] = (job.tap_dy[t] - dylo) * L.seg_alloc + (job.tap_dx[t] - dxlo); }
-    std::sort(order, order + job.ntaps, [&](int a, int b) { return key[a] < key[b]; });
-    L.npairs = (job.ntaps + 1) / 2;
+    for (int t = 0; t < ntaps; ++t) { order[t] = t; key[t] = (tdy[t] - dylo) * L.seg_alloc + (tdx[t] - dxlo); }
+    std::sort(order, order + ntaps, [&](int a, int b) { return key[a] < key[b]; });
+    L.npairs = (ntaps + 1) / 2;
     for (int a = 0; a < L.npairs; ++a) {
-        const int t1 = order[2 * a], t2 = 2 * a + 1 < job.ntaps ? order[2 * a + 1] : -1;
+        const int t1 = order[2 * a], t2 = 2 * a + 1 < ntaps ? order[2 * a + 1] : -1;
         L.pair_t1[a] = t1; L.pair_t2[a] = t2;
-        L.pair_seg[a] = job.tap_dy[t1] - dylo; L.pair_off[a] = job.tap_dx[t1] - dxlo;
+        L.pair_seg[a] = tdy[t1] - dylo; L.pair_off[a] = tdx[t1] - dxlo;
         L.pair_lbo[a] = t2 >= 0 ? (key[t2] - key[t1]) * 128 : 1024;
         if (L.pair_lbo[a] <= 0 || L.pair_lbo[a] >= (1 << 18)) throw std::logic_error("wgrad_tc: tap pair distance out of range");
+        if (full3)   // position p of DY at shift s pairs with X[p - s + dy*P + 1]: dx = 1 - s
+            for (int h = 0; h < 2; ++h)
+                for (int sft = 0; sft < 3; ++sft) {
+                    const int ts = h ? t2 : t1;
+                    L.sh_tap[a][h][sft] = ts >= 0 ? grid3[tdy[ts] + 1][(1 - sft) + 1] : -1;
+                }
     }
+    L.shift = full3 ? 1 : 0;
+    L.Nmma = full3 ? 48 : L.N;
     int cols = 32;
-    while (cols < L.npairs * L.N) cols *= 2;
+    while (cols < L.npairs * L.Nmma) cols *= 2;
     L.tmem_cols = cols;
     L.cxtiles = (job.cx + 63) / 64;
     L.nsplit = (int)std::max<long long>(1, std::min<long long>(L.chunks, kMaxSplitTilesTc / L.cxtiles));
@@ -298,7 +331,8 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     L.out = job.out; L.sy = job.sy; L.sx = job.sx;
     L.cy_real = job.cy_real ? job.cy_real : job.cy; L.cx_real = job.cx_real ? job.cx_real : job.cx;
     make_tensor_map_2d(&L.tmX, job.x, job.g.positions(), job.x_ctot, 64, L.seg_alloc);
-    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, 64, L.kw);
+    // shift mode: three [kw][16] sub-tiles (32-byte rows, 32-byte swizzle), one per shift
+    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, L.shift ? 16 : 64, L.kw);
     const double px = (double)job.g.N * job.g.H * job.g.W;
     L.flops = 2.0 * px * L.cx_real * L.cy_real * job.ntaps;
     L.bytes = 2.0 * px * (job.cx + job.cy);

@@ -101,7 +101,8 @@ int padded_k(int cin);             // multiple of 64
 int padded_n(int cout);            // multiple of 16
 size_t packed_filter_elems(int cin, int npad_total, int ntaps);
 void setup_conv(ConvLaunch& L, const ConvSetup& s);
-void launch_conv(const ConvLaunch& L, cudaStream_t st);
+// rev: the CTAs walk the work items downwards (see bn_stats_nhwc)
+void launch_conv(const ConvLaunch& L, cudaStream_t st, int rev = 0);
 
 // packed[tap][n][k] = (n < nreal && k < kreal) ? w[n*sn + k*sk + tapmap[tap]] : 0,   n < npad_total, k < padded_k(kreal)
 void pack_filters_bf16(const float* w, bf16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
@@ -129,7 +130,8 @@ struct ViewF {   // same, fp32 elements (the conv outputs z that feed a batch no
     int ctot = 0, c0 = 0, C = 0;
 };
 // sums[c] = sum x, sums[C + c] = sum x^2 over all positions of x = mish_first ? mish(z) : z (pads are zero and add nothing)
-void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st);
+// rev (all bn passes): walk the positions downwards, so that a pass starts where its producer stopped (L2 reuse)
+void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev = 0);
 // y = mish_first ? gamma*(mish(z)-mean)*invstd+beta : mish(gamma*(z-mean)*invstd+beta)   [mish optional]; pads are left alone
 // Optional fused bn_finalize (kernels_bn.cu): every CTA derives mean / invstd from the layer's sums itself, CTA 0 also
 // updates the running statistics, the saved stats and the device-side num_updates counter (layers.h:1392-1397).
@@ -142,15 +144,15 @@ struct BnFinalize {
     float* stats_out = nullptr;     // [2][C] mean, invstd for the backward pass
 };
 void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, int has_mish, const float* gamma, const float* beta,
-                   const float* stats, cudaStream_t st, const BnFinalize* fin = nullptr);
+                   const float* stats, cudaStream_t st, const BnFinalize* fin = nullptr, int rev = 0);
 // backward pass 1 (cpu_dlib.cpp:1228-1250): red[c] = sum dv, red[C + c] = sum dv*xhat
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
-                             const float* beta, const float* stats, double* red, cudaStream_t st);
+                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev = 0);
 // backward pass 2 (cpu_dlib.cpp:1252-1288): dz = gradient at the conv output (bf16, pads untouched), dgamma/dbeta from `red`,
 // dbias[c] = sum dz (assign_conv_bias_gradient, cpu_dlib.cpp:470-504; dbias must be zeroed by the caller)
 void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, const Geo& g, int mish_first, int has_mish, const float* gamma,
                             const float* beta, const float* stats, const double* red, float* dgamma, float* dbeta, float* dbias,
-                            cudaStream_t st);
+                            cudaStream_t st, int rev = 0);
 // g[c] += sum over positions of v (caller zeroes g)
 void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st);
 // max_pool_<3,3,2,2,0,0> gradient (cpu_dlib.cpp:1971-2017): the first maximum of a window in row-major order receives it; gin +=
@@ -200,6 +202,11 @@ struct WgradTcLaunch {
     int pair_seg[5] = {0}, pair_off[5] = {0}, pair_lbo[5] = {0};   // segment (relative to the run) and row offset of t1; byte distance to t2
     int pair_t1[5] = {0}, pair_t2[5] = {0};                          // tap ids (t2 = -1: none)
     int N = 16;                       // padded cy
+    // 3x3, cy <= 16 ("shift" mode): the three dx taps ride on B instead of A -- DY is staged three times, shifted by 0, 1, 2
+    // positions, as the three 16-channel atoms of one N = 48 operand, so one MMA against X[p + dy*P + 1] yields dx = +1, 0, -1
+    // at once: two MMAs (dy pair, single dy) per 16 positions instead of five.
+    int shift = 0, Nmma = 16;
+    int sh_tap[5][2][3] = {};         // [accumulator][rows 0-63 / 64-127][shift] -> tap id or -1
     int stages = 2, tmem_cols = 64;
     unsigned x_stage_bytes = 0, stage_bytes = 0, smem_bytes = 0;
     long long chunks = 0;
