@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
 
     if (warp == 0) {
         if (elect_one()) {
-            const uint32_t tx = L.x_stage_bytes + (uint32_t)(L.th * L.kw) * (L.shift ? 96u : 128u);
+            const uint32_t tx = L.x_stage_bytes + (uint32_t)L.th * (L.shift ? (uint32_t)(L.kw + 8) * 32u : (uint32_t)L.kw * 128u);
             uint32_t it = 0;
             for (long long chunk = c_begin; chunk < c_end; ++chunk, ++it) {
                 const int s = it % L.stages;
@@ -131,10 +131,8 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 for (int sg = 0; sg < L.nseg; ++sg)
                     tma_2d(xs + (uint32_t)(sg * L.seg_alloc) * 128u, &L.tmX, L.x_c0 + cxt * 64, o0 + L.seg_pos[sg], &full_bar[s]);
                 for (int m = 0; m < L.th; ++m) {
-                    if (L.shift) {
-                        for (int sft = 0; sft < 3; ++sft)
-                            tma_2d(ys + (uint32_t)((m * 3 + sft) * L.kw) * 32u, &L.tmY, L.dy_c0, o0 + m * L.run_stride + sft, &full_bar[s]);
-                    } else tma_2d(ys + (uint32_t)(m * L.kw) * 128u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
+                    if (L.shift) tma_2d(ys + (uint32_t)(m * (L.kw + 8)) * 32u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
+                    else tma_2d(ys + (uint32_t)(m * L.kw) * 128u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
                 }
             }
         }
@@ -160,8 +158,9 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 const uint32_t xs16 = (smem0 + (uint32_t)s * L.stage_bytes) >> 4, ys16 = xs16 + (L.x_stage_bytes >> 4);
                 for (int m = 0; m < L.th; ++m)
                     for (int kk = 0; kk < ksteps; ++kk) {
-                        // shift mode: three 16-channel atoms (one per shift), LBO = one [kw][16] sub-tile apart, 32-byte rows
-                        const uint32_t b_lo = L.shift ? (ys16 + (uint32_t)(m * 3 * L.kw + kk * 16) * 2u) | ((uint32_t)(L.kw * 2) << 16)
+                        // shift mode: three 16-channel atoms (one per shift) ONE ROW apart (LBO = 32 bytes) in the same staged tile;
+                        // the swizzle works on absolute shared-memory addresses, so a row offset keeps matching what TMA wrote
+                        const uint32_t b_lo = L.shift ? (ys16 + (uint32_t)(m * (L.kw + 8) + kk * 16) * 2u) | (2u << 16)
                                                       : (ys16 + (uint32_t)(m * L.kw + kk * 16) * 8u) | (1u << 16);
                         const uint32_t a_base = xs16 + (uint32_t)(m * L.seg_alloc + kk * 16) * 8u;
                         const uint32_t acc = (uint32_t)(it | m | kk);
@@ -278,10 +277,10 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     double best = 1e300;
     auto consider = [&](int rows_mode, int kw, int th) {
         const int nseg = th + dyr, seg_alloc = (kw + dxr + 7) / 8 * 8;
-        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = (xb + (size_t)th * kw * (full3 ? 96 : 128) + 1023) / 1024 * 1024;
+        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = (xb + (size_t)th * (full3 ? (kw + 8) * 32 : kw * 128) + 1023) / 1024 * 1024;
         if (nseg > 12 || seg_alloc > 256 || 2 * sb + 1024 > budget) return;
         const int stages = (int)std::min<size_t>(kWMaxStages, (budget - 1024) / sb);
-        const double score = (double)(nseg * seg_alloc + th * kw) / (th * kw) * (stages >= 3 ? 1.0 : 1.15);
+        const double score = (double)(nseg * seg_alloc + th * (full3 ? kw + 8 : kw)) / (th * kw) * (stages >= 3 ? 1.0 : 1.15);
         if (score < best) {
             best = score;
             L.rows_mode = rows_mode; L.kw = kw; L.th = th; L.nseg = nseg; L.seg_alloc = seg_alloc;
@@ -331,8 +330,8 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     L.out = job.out; L.sy = job.sy; L.sx = job.sx;
     L.cy_real = job.cy_real ? job.cy_real : job.cy; L.cx_real = job.cx_real ? job.cx_real : job.cx;
     make_tensor_map_2d(&L.tmX, job.x, job.g.positions(), job.x_ctot, 64, L.seg_alloc);
-    // shift mode: three [kw][16] sub-tiles (32-byte rows, 32-byte swizzle), one per shift
-    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, L.shift ? 16 : 64, L.kw);
+    // shift mode: one [kw + 8][16] tile per run (32-byte rows, 32-byte swizzle); the three shifts are row offsets into it
+    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, L.shift ? 16 : 64, L.shift ? L.kw + 8 : L.kw);
     const double px = (double)job.g.N * job.g.H * job.g.W;
     L.flops = 2.0 * px * L.cx_real * L.cy_real * job.ntaps;
     L.bytes = 2.0 * px * (job.cx + job.cy);
