@@ -291,7 +291,18 @@ def own_arm(args):
     else:
         achieved = top["bytes"] / (top["ms"] * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"]}
-    roof.update({"traffic": None, "kernel": top["name"], "avg_launch_ms": avg_ms, "share_of_step": top["ms"] / total_ms,
+    # DRAM traffic per launch of the dominant family: ncu dram__bytes_read.sum + dram__bytes_write.sum over every launch of one step,
+    # averaged per launch like `achieved` (profiles/r01_traffic.json, written from the committed ncu csv by profiles/traffic_from_ncu.py)
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+            tj = json.load(f)
+        ent = tj.get("bf16" if precision != ab.AB_PRECISION_FP32 else "fp32", {}).get(top["name"])
+        if ent:
+            traffic, traffic_src = ent["dram_bytes_per_launch"], tj.get("source")
+    except (OSError, ValueError, KeyError):
+        pass
+    roof.update({"traffic": traffic, "traffic_source": traffic_src, "kernel": top["name"], "avg_launch_ms": avg_ms, "share_of_step": top["ms"] / total_ms,
                  "peak_source": pk["source"] + (" (sustained bf16 cuBLAS)" if tensor_bound else " (copy)")})
     families = {f["name"]: {"launches_per_step": f["launches"] / args.steps, "ms_per_step": f["ms"] / args.steps,
                             "tflops": f["flops"] / (f["ms"] * 1e-3) / 1e12 if f["flops"] else None,
