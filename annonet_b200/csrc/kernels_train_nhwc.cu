@@ -460,13 +460,15 @@ __global__ void __launch_bounds__(256) pack_batched_kernel(const float* __restri
 }
 
 struct Shape { dim3 block; unsigned grid; };
-Shape channel_shape(int C, long long npos)
+// ctas_per_sm: the kernel's residency (__launch_bounds__): a grid of exactly the resident CTAs runs as ONE wave of equal
+// grid-stride shares -- no partially filled last wave, and the per-CTA prologues (constants, fused bn_finalize) run once per slot
+Shape channel_shape(int C, long long npos, int ctas_per_sm = 8)
 {
     const int C8 = C / 8;
     if (C % 8 || C8 < 1 || C8 > 32) throw std::invalid_argument("bf16 NHWC kernels need 8 <= C <= 256, C % 8 == 0");
     const int TY = kMaxT / C8;
     const long long want = (npos + TY - 1) / TY;
-    return Shape{dim3(C8, TY), (unsigned)std::max<long long>(1, std::min<long long>(want, k::kNumSMs * 8))};
+    return Shape{dim3(C8, TY), (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)k::kNumSMs * ctas_per_sm))};
 }
 
 }  // namespace
@@ -476,7 +478,7 @@ void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, c
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 3.0 * g.N * g.H * g.W * z.C, 2.0 * g.N * g.H * g.W * z.C, st);
     cudaMemsetAsync(sums, 0, sizeof(double) * 2 * z.C, st);
-    const Shape s = channel_shape(z.C, d.total);
+    const Shape s = channel_shape(z.C, d.total, 4);
     bn_stats_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, d.total, mish_first, sums, rev);
     k::count_launch();
 }
@@ -486,7 +488,7 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
-    const Shape s = channel_shape(z.C, d.total);
+    const Shape s = channel_shape(z.C, d.total, 4);
     bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
     k::count_launch();
 }
@@ -497,7 +499,7 @@ void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int m
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 6.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
     cudaMemsetAsync(red, 0, sizeof(double) * 2 * z.C, st);
-    const Shape s = channel_shape(z.C, d.total);
+    const Shape s = channel_shape(z.C, d.total, 3);
     bn_bwd_reduce_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, d.total, mish_first, has_mish, gamma, beta, stats,
                                                      red, rev);
     k::count_launch();
@@ -509,7 +511,7 @@ void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, cons
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 8.0 * g.N * g.H * g.W * z.C, 6.0 * g.N * g.H * g.W * z.C, st);
-    const Shape s = channel_shape(z.C, d.total);
+    const Shape s = channel_shape(z.C, d.total, 3);
     const float invnum = 1.0f / (float)((long long)g.N * g.H * g.W);
     bn_bwd_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, dz.p, dz.ctot, dz.c0, d, mish_first, has_mish, gamma, beta, stats, red,
                                                     invnum, dgamma, dbeta, dbias, rev);
