@@ -116,8 +116,8 @@ private:
     std::unique_ptr<TcState> tc_;
 
     int device_, precision_;
-    cudaStream_t stream_ = nullptr, comm_stream_ = nullptr;
-    cudaEvent_t ev_bucket_[8] = {}, ev_comm_done_ = nullptr, ev_stage_ = nullptr;
+    cudaStream_t stream_ = nullptr, comm_stream_ = nullptr, copy_stream_ = nullptr;
+    cudaEvent_t ev_bucket_[8] = {}, ev_comm_done_ = nullptr, ev_stage_ = nullptr, ev_unstaged_ = nullptr;
     bool loaded_ = false;
     NetModel model_;  // host copy of the structure (+ parameters as loaded; device is authoritative after load)
     Plan plan_;
@@ -136,7 +136,7 @@ private:
 
     // training workspace
     Levels tw_act_, tw_grad_;
-    DevBuf t_x_, t_logits_, t_glogits_, t_z_, t_pool_, t_dz_, t_dpool_, t_dead_, t_stats_, t_sums_, t_scratch_, t_imgs_, t_labels_,
+    DevBuf t_x_, t_logits_, t_glogits_, t_z_, t_pool_, t_dz_, t_dpool_, t_dead_, t_stats_, t_sums_, t_scratch_, t_imgs_, t_labels_, t_stage_dev_,
         t_loss_;
     std::vector<size_t> z_off_, pool_off_, stats_off_;
     int tn_ = 0, th_ = 0, tw_ = 0;

@@ -77,9 +77,11 @@ Engine::Engine(int device, int precision) : device_(device), precision_(precisio
     AB_CUDA(cudaSetDevice(device_));
     AB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
     AB_CUDA(cudaStreamCreateWithFlags(&comm_stream_, cudaStreamNonBlocking));
+    AB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
     for (auto& ev : ev_bucket_) AB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     AB_CUDA(cudaEventCreateWithFlags(&ev_comm_done_, cudaEventDisableTiming));
     AB_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
+    AB_CUDA(cudaEventCreateWithFlags(&ev_unstaged_, cudaEventDisableTiming));
     AB_CUDA(cudaMallocHost((void**)&loss_host_, sizeof(double)));
     *loss_host_ = 0;
 }
@@ -92,9 +94,11 @@ Engine::~Engine()
     for (auto& ev : ev_bucket_) if (ev) cudaEventDestroy(ev);
     if (ev_comm_done_) cudaEventDestroy(ev_comm_done_);
     if (ev_stage_) cudaEventDestroy(ev_stage_);
+    if (ev_unstaged_) cudaEventDestroy(ev_unstaged_);
     if (pinned_) cudaFreeHost(pinned_);
     if (loss_host_) cudaFreeHost(loss_host_);
     if (comm_stream_) cudaStreamDestroy(comm_stream_);
+    if (copy_stream_) cudaStreamDestroy(copy_stream_);
     if (stream_) cudaStreamDestroy(stream_);
 }
 

@@ -236,16 +236,23 @@ void Engine::train_step_host(const uint8_t* imgs, const void* labels, int n, int
     AB_CUDA(cudaSetDevice(device_));
     level_dims(h, w, plan_.levels);
     const size_t ib = (size_t)n * h * w * 3, lb = (size_t)n * h * w * 8;
-    // depth-1 asynchrony (trainer.h:87,1252): the staging buffer is reused once the previous step's copy has drained
-    AB_CUDA(cudaEventSynchronize(ev_stage_));
+    // depth-1 asynchrony (trainer.h:87,1252).  The host->device copy of step i+1 runs on its own stream WHILE step i computes:
+    // pinned staging -> device staging (copy stream), then a device-to-device copy into the step's fixed input buffers (the
+    // CUDA graph of the step is keyed on those pointers) at the head of the compute stream.
+    AB_CUDA(cudaEventSynchronize(ev_stage_));            // the previous step's copy has left the pinned buffer
     char* stage = (char*)pinned(ib + lb);
     std::memcpy(stage, imgs, ib);
     std::memcpy(stage + ib, labels, lb);
     t_imgs_.reserve(ib);
     t_labels_.reserve(lb);
-    AB_CUDA(cudaMemcpyAsync(t_imgs_.p, stage, ib, cudaMemcpyHostToDevice, stream_));
-    AB_CUDA(cudaMemcpyAsync(t_labels_.p, stage + ib, lb, cudaMemcpyHostToDevice, stream_));
-    AB_CUDA(cudaEventRecord(ev_stage_, stream_));
+    t_stage_dev_.reserve(ib + lb);
+    AB_CUDA(cudaStreamWaitEvent(copy_stream_, ev_unstaged_, 0));   // the previous step has emptied the device staging buffer
+    AB_CUDA(cudaMemcpyAsync(t_stage_dev_.p, stage, ib + lb, cudaMemcpyHostToDevice, copy_stream_));
+    AB_CUDA(cudaEventRecord(ev_stage_, copy_stream_));
+    AB_CUDA(cudaStreamWaitEvent(stream_, ev_stage_, 0));
+    AB_CUDA(cudaMemcpyAsync(t_imgs_.p, t_stage_dev_.p, ib, cudaMemcpyDeviceToDevice, stream_));
+    AB_CUDA(cudaMemcpyAsync(t_labels_.p, (const char*)t_stage_dev_.p + ib, lb, cudaMemcpyDeviceToDevice, stream_));
+    AB_CUDA(cudaEventRecord(ev_unstaged_, stream_));
     train_step_device(t_imgs_.as<uint8_t>(), t_labels_.p, n, h, w, update);
 }
 
