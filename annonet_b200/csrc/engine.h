@@ -112,7 +112,8 @@ private:
     void tc_pack_forward_filters();
     void tc_ensure_train(int n, int h, int w);
     void tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
-    void tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);
+    void tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update, bool capture);
+    void tc_close_segment();
     std::unique_ptr<TcState> tc_;
 
     int device_, precision_;

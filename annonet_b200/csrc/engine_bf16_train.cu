@@ -297,51 +297,67 @@ void Engine::level_values(int level, bool gradient, std::vector<float>& out, int
 // one.  The step is static (shapes, pointers, the bn counters live on the device), so it is captured once into a CUDA
 // graph and replayed while nothing it bakes in changes (TcState::GraphKey).  Not captured: the first step of a
 // configuration (lazy module loading, cudaFuncSetAttribute), per-kernel profiling, Adam (its step counter is a kernel
-// argument) and data-parallel runs (NCCL runs on the side stream, eagerly).
+// argument).  Data-parallel runs capture the step as segments split at the gradient-bucket boundaries and issue the NCCL
+// all-reduces eagerly between them (TcState::graph_segs).
 void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
 {
     if (n < 2) throw std::invalid_argument("training needs a mini-batch of at least 2 (bn_ runs in batch mode only for num_samples > 1, layers.h:1392)");
     tc_ensure_train(n, h, w);
     TcState& T = *tc_;
     static const bool no_graph = getenv("AB_NO_GRAPH") != nullptr;
-    // data parallel: steps run eagerly -- capturing the bucketed all-reduces (fork to the communication stream, join before
-    // the update) hung on the 2-GPU box with the torch-bundled NCCL 2.28; AB_GRAPH_NCCL=1 re-enables the attempt
-    static const bool no_graph_nccl = getenv("AB_GRAPH_NCCL") == nullptr;
-    if (no_graph || k::prof_enabled() || (world_ > 1 && no_graph_nccl) || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update); return; }
+    if (no_graph || k::prof_enabled() || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update, false); return; }
     TcState::GraphKey key;
     key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
     key.lr = hyper.learning_rate; key.wd = hyper.weight_decay; key.momentum = hyper.momentum; key.window = window_.empty() ? 0 : window_[0];
-    if (T.graph_exec && T.graph_key == key) {
-        AB_CUDA(cudaGraphLaunch(T.graph_exec, stream_));
-        k::count_launch((int)T.graph_kernels);
-        return;
+    if (!(T.graph_segs.size() && T.graph_key == key)) {
+        if (!(T.seen_key == key)) {   // first time: run eagerly
+            T.seen_key = key;
+            tc_train_body(imgs_dev, labels_dev, n, h, w, update, false);
+            return;
+        }
+        T.drop_graph();
+        const unsigned long long k0 = k::g_launches.load();
+        AB_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
+        try {
+            tc_train_body(imgs_dev, labels_dev, n, h, w, update, true);   // closes a segment at every bucket boundary
+            tc_close_segment();
+        } catch (...) {
+            cudaGraph_t graph = nullptr;
+            cudaStreamEndCapture(stream_, &graph);
+            if (graph) cudaGraphDestroy(graph);
+            T.drop_graph();
+            throw;
+        }
+        T.graph_kernels = k::g_launches.load() - k0;
+        T.graph_key = key;
     }
-    if (!(T.seen_key == key)) {   // first time: run eagerly
-        T.seen_key = key;
-        tc_train_body(imgs_dev, labels_dev, n, h, w, update);
-        return;
+    // replay: segment, bucket all-reduce (eager, communication stream), ..., join, last segment (optimizer step)
+    for (size_t i = 0; i < T.graph_segs.size(); ++i) {
+        AB_CUDA(cudaGraphLaunch(T.graph_segs[i], stream_));
+        if (i < T.graph_buckets.size()) {
+            allreduce_range(T.graph_buckets[i].first, T.graph_buckets[i].second);
+            if (i + 1 == T.graph_buckets.size()) {
+                AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
+                AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
+            }
+        }
     }
-    if (T.graph_exec) { cudaGraphExecDestroy(T.graph_exec); T.graph_exec = nullptr; }
-    const unsigned long long k0 = k::g_launches.load();
-    cudaGraph_t graph = nullptr;
-    AB_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
-    try {
-        tc_train_body(imgs_dev, labels_dev, n, h, w, update);
-    } catch (...) {
-        cudaStreamEndCapture(stream_, &graph);
-        if (graph) cudaGraphDestroy(graph);
-        throw;
-    }
-    AB_CUDA(cudaStreamEndCapture(stream_, &graph));
-    T.graph_kernels = k::g_launches.load() - k0;
-    const cudaError_t e = cudaGraphInstantiate(&T.graph_exec, graph, 0);
-    cudaGraphDestroy(graph);
-    AB_CUDA(e);
-    T.graph_key = key;
-    AB_CUDA(cudaGraphLaunch(T.graph_exec, stream_));
+    k::count_launch((int)T.graph_kernels);
 }
 
-void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
+// ends the capture running on the compute stream and keeps it as the next segment of the step
+void Engine::tc_close_segment()
+{
+    cudaGraph_t graph = nullptr;
+    AB_CUDA(cudaStreamEndCapture(stream_, &graph));
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    AB_CUDA(e);
+    tc_->graph_segs.push_back(exec);
+}
+
+void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update, bool capture)
 {
     TcState& T = *tc_;
     const float* P = params_.as<float>();
@@ -406,6 +422,14 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
     const size_t np = plan_.num_params;
     k::fill_zero(G, np * sizeof(float), stream_);
     const int nbuckets = 4;
+    // eager: all-reduce the bucket now;  capturing: the bucket ends a graph segment (tc_train_step issues the all-reduce at replay)
+    auto bucket_ready = [&](size_t lo, size_t hi) {
+        if (!capture) { allreduce_range(lo, hi); return; }
+        if (world_ <= 1 || hi <= lo) return;
+        tc_close_segment();
+        T.graph_buckets.emplace_back(lo, hi);
+        AB_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
+    };
     size_t bucket_hi = np;
     for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
         const ConvGroup& g = plan_.groups[gi];
@@ -447,14 +471,16 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             }
         }
         if (world_ > 1 && bucket_hi - g.w_off >= np / nbuckets) {
-            allreduce_range(g.w_off, bucket_hi);
+            bucket_ready(g.w_off, bucket_hi);
             bucket_hi = g.w_off;
         }
     }
     if (world_ > 1) {
-        allreduce_range(0, bucket_hi);
-        AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
-        AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
+        bucket_ready(0, bucket_hi);
+        if (!capture) {
+            AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
+            AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
+        }
     }
     if (update) optimizer_step();
     AB_CUDA(cudaMemcpyAsync(loss_host_, t_loss_.p, sizeof(double), cudaMemcpyDeviceToHost, stream_));

@@ -67,9 +67,14 @@ struct TcState {
         }
     };
     GraphKey graph_key, seen_key;
-    cudaGraphExec_t graph_exec = nullptr;
+    // Data parallel: the step is captured as SEGMENTS split at the gradient-bucket boundaries; the NCCL all-reduce of bucket i
+    // is issued eagerly on the communication stream between segment i and i+1 (NCCL inside a capture hung on the 2-GPU box).
+    // One process: a single segment.
+    std::vector<cudaGraphExec_t> graph_segs;
+    std::vector<std::pair<size_t, size_t>> graph_buckets;   // arena range all-reduced after segment i (segs.size() - 1 entries)
     unsigned long long graph_kernels = 0;   // kernels inside the graph (for ab_kernel_launches)
-    ~TcState() { if (graph_exec) cudaGraphExecDestroy(graph_exec); }
+    void drop_graph() { for (cudaGraphExec_t e : graph_segs) cudaGraphExecDestroy(e); graph_segs.clear(); graph_buckets.clear(); }
+    ~TcState() { drop_graph(); }
 };
 
 // prepared launches of one conv group in the forward direction (engine_bf16.cu)
