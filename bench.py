@@ -16,6 +16,7 @@ forward + loss + backward + update over one synthetic minibatch.
 Also reported (not the headline): tiled inference of one 1024 x 1024 image (configs[0]) in Mpix/s.
 """
 import argparse
+import atexit
 import json
 import os
 import subprocess
@@ -51,23 +52,36 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.t0, self.t1 = index, None, [], None, None
 
-    def __enter__(self):
+    def start(self):
+        """Started well before the timed region: nvidia-smi needs > 1 s to come up on an 8-GPU box."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
+            atexit.register(self._kill)   # an early exit must not leave the sampler looping
         except Exception:
             self.proc = None
         return self
 
+    def _kill(self):
+        if self.proc and self.proc.poll() is None:
+            self.proc.kill()
+
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def __enter__(self):   # the timed region
+        if self.proc is None:
+            self.start()
+        self.t0 = time.perf_counter()
+        return self
 
     def __exit__(self, *a):
+        self.t1 = time.perf_counter()
         if self.proc:
             time.sleep(0.12)
             self.proc.terminate()
@@ -80,7 +94,13 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        # samples that arrived during the timed region (a sample is up to 20 ms old); if the region was shorter than the
+        # sampling could resolve, the samples taken under the warm-up load just before it
+        inside = [ln for t, ln in self.lines if self.t0 is not None and self.t0 <= t <= self.t1 + 0.03]
+        window = "timed region"
+        if not inside:
+            inside, window = [ln for t, ln in self.lines if self.t0 is None or t >= self.t0 - 0.5], "warm-up + timed region"
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -93,7 +113,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 def synthetic_batch(n, h, w, k, seed):
@@ -179,6 +199,7 @@ def own_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the engine has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
+    clocks = ClockSampler(local).start()   # long before the timed region (nvidia-smi start-up)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     precision = ab.AB_PRECISION_BF16 if args.precision == "bf16" else ab.AB_PRECISION_FP32
@@ -219,7 +240,7 @@ def own_arm(args):
     launches0 = net.kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    with ClockSampler(local) as clocks:
+    with clocks:
         e0.record(stream)
         for _ in range(args.steps):
             step_device()
