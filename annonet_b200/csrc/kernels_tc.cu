@@ -298,6 +298,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                     valid = valid && r >= 1 && c >= 1;
                     opos = (long long)n * L.S + (long long)r * P + c;
                 }
+                // Stores go out in lane PAIRS: lanes 2k and 2k+1 together write a whole 32-byte sector of row A (lane 2k's
+                // position), then of row B, instead of a 16-byte half sector of their own row each -- half the L1 -> crossbar
+                // sector requests (ncu: l1tex2xbar request cycles 71 % on the level-0 forward convolutions).
+                const bool odd = lane & 1;
+                const long long opos_p = __shfl_xor_sync(0xffffffffu, opos, 1);
+                const bool valid_p = __shfl_xor_sync(0xffffffffu, (int)valid, 1) != 0;
+                const long long posA = odd ? opos_p : opos, posB = odd ? opos : opos_p;
+                const bool okA = odd ? valid_p : valid, okB = odd ? valid : valid_p;
                 for (int j = jpar > 0 ? 16 : 0; j < nblk; j += jpar >= 0 ? 32 : 16) {
                     float v[16];
                     if (NTAPS == 9 && L.kym) {
@@ -315,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         tmem_ld_fence(v);
                     }
                     const int co0 = n0 + j;
-                    if (!valid || co0 >= L.cout) continue;
+                    if (co0 >= L.cout) continue;   // (uniform) padding columns only
 #pragma unroll
                     for (int i4 = 0; i4 < 4; ++i4) {
                         const float4 b = *reinterpret_cast<const float4*>(&s_bias[co0 + 4 * i4]);
@@ -334,38 +342,70 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                             }
                         }
                     }
-                    if (L.mode == OUT_F32_NHWC) {
-                        float4* o = reinterpret_cast<float4*>((float*)L.out + opos * L.out_ctot + L.out_c0 + co0);
+                    if (L.mode == OUT_F32_NCHW) {
+                        // fp32 planes (the logits): consecutive lanes are consecutive pixels of a plane already
+                        if (valid) {
+                            const long long hw = (long long)L.H * L.W;
+                            float* o = (float*)L.out + ((long long)n * L.cout) * hw + (long long)(r - 1) * L.W + (c - 1);
 #pragma unroll
-                        for (int i4 = 0; i4 < 4; ++i4)
-                            if (co0 + 4 * i4 < L.cout) o[i4] = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
-                    } else if (L.mode == OUT_F32_NCHW) {
-                        const long long hw = (long long)L.H * L.W;
-                        float* o = (float*)L.out + ((long long)n * L.cout) * hw + (long long)(r - 1) * L.W + (c - 1);
+                            for (int i = 0; i < 16; ++i)
+                                if (co0 + i < L.cout) o[(long long)(co0 + i) * hw] = v[i];
+                        }
+                    } else if (L.mode == OUT_F32_NHWC) {
+                        // row = four 16-byte quarters Q0..Q3; even lane writes Q0, Q2 of both rows, odd lane Q1, Q3
+                        float rcv[8];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (co0 + i < L.cout) o[(long long)(co0 + i) * hw] = v[i];
+                        for (int i = 0; i < 4; ++i) {
+                            rcv[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i] : v[4 + i], 1);
+                            rcv[4 + i] = __shfl_xor_sync(0xffffffffu, odd ? v[8 + i] : v[12 + i], 1);
+                        }
+                        const int qo = odd ? 4 : 0;
+                        float* oa = (float*)L.out + posA * L.out_ctot + L.out_c0 + co0 + qo;
+                        float* ob = (float*)L.out + posB * L.out_ctot + L.out_c0 + co0 + qo;
+                        const bool c0ok = co0 + qo < L.cout, c1ok = co0 + 8 + qo < L.cout;
+                        if (okA && c0ok) *reinterpret_cast<float4*>(oa) = odd ? make_float4(rcv[0], rcv[1], rcv[2], rcv[3]) : make_float4(v[0], v[1], v[2], v[3]);
+                        if (okA && c1ok) *reinterpret_cast<float4*>(oa + 8) = odd ? make_float4(rcv[4], rcv[5], rcv[6], rcv[7]) : make_float4(v[8], v[9], v[10], v[11]);
+                        if (okB && c0ok) *reinterpret_cast<float4*>(ob) = odd ? make_float4(v[4], v[5], v[6], v[7]) : make_float4(rcv[0], rcv[1], rcv[2], rcv[3]);
+                        if (okB && c1ok) *reinterpret_cast<float4*>(ob + 8) = odd ? make_float4(v[12], v[13], v[14], v[15]) : make_float4(rcv[4], rcv[5], rcv[6], rcv[7]);
                     } else {
-                        // channel counts are multiples of 8: 16-byte vector stores of 8 channels
-                        bf16* o = (bf16*)L.out + opos * L.out_ctot + L.out_c0 + co0;
+                        // bf16 row block = two 16-byte halves (8 channels each); even lane writes half 0 of both rows, odd lane half 1
+                        const int ho = odd ? 8 : 0;
+                        const bool cok = co0 + ho < L.cout;
+                        bf16* oa = (bf16*)L.out + posA * L.out_ctot + L.out_c0 + co0 + ho;
+                        bf16* ob = (bf16*)L.out + posB * L.out_ctot + L.out_c0 + co0 + ho;
+                        if (accum) {
+                            uint4 oldA = make_uint4(0, 0, 0, 0), oldB = make_uint4(0, 0, 0, 0);
+                            if (okA && cok) oldA = *reinterpret_cast<const uint4*>(oa);
+                            if (okB && cok) oldB = *reinterpret_cast<const uint4*>(ob);
+                            float rcv[8];
 #pragma unroll
-                        for (int h8 = 0; h8 < 2; ++h8) {
-                            if (co0 + h8 * 8 >= L.cout) break;
-                            uint4* dst = reinterpret_cast<uint4*>(o + h8 * 8);
-                            __nv_bfloat162 pk[4];
-                            if (accum) {
-                                const uint4 old = *dst;
-                                const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&old);
+                            for (int i = 0; i < 8; ++i) rcv[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i] : v[8 + i], 1);
+                            const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&oldA);
+                            const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&oldB);
+                            __nv_bfloat162 ra[4], rb[4];
 #pragma unroll
-                                for (int i = 0; i < 4; ++i) {
-                                    const float2 f = __bfloat1622float2(ob[i]);
-                                    pk[i] = __floats2bfloat162_rn(f.x + v[h8 * 8 + 2 * i], f.y + v[h8 * 8 + 2 * i + 1]);
-                                }
-                            } else {
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) pk[i] = __floats2bfloat162_rn(v[h8 * 8 + 2 * i], v[h8 * 8 + 2 * i + 1]);
+                            for (int i = 0; i < 4; ++i) {
+                                const float2 fa = __bfloat1622float2(pa[i]), fb = __bfloat1622float2(pb[i]);
+                                // row A's values: odd lane got them from its partner; row B's: even lane did
+                                const float a0 = odd ? rcv[2 * i] : v[2 * i], a1 = odd ? rcv[2 * i + 1] : v[2 * i + 1];
+                                const float b0 = odd ? v[8 + 2 * i] : rcv[2 * i], b1 = odd ? v[8 + 2 * i + 1] : rcv[2 * i + 1];
+                                ra[i] = __floats2bfloat162_rn(fa.x + a0, fa.y + a1);
+                                rb[i] = __floats2bfloat162_rn(fb.x + b0, fb.y + b1);
                             }
-                            *dst = *reinterpret_cast<const uint4*>(pk);
+                            if (okA && cok) *reinterpret_cast<uint4*>(oa) = *reinterpret_cast<const uint4*>(ra);
+                            if (okB && cok) *reinterpret_cast<uint4*>(ob) = *reinterpret_cast<const uint4*>(rb);
+                        } else {
+                            __nv_bfloat162 pk[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) pk[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                            const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
+                            uint32_t rc[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) rc[i] = __shfl_xor_sync(0xffffffffu, odd ? pw[i] : pw[4 + i], 1);
+                            const uint4 mine0 = make_uint4(pw[0], pw[1], pw[2], pw[3]), mine1 = make_uint4(pw[4], pw[5], pw[6], pw[7]);
+                            const uint4 got = make_uint4(rc[0], rc[1], rc[2], rc[3]);
+                            if (okA && cok) *reinterpret_cast<uint4*>(oa) = odd ? got : mine0;
+                            if (okB && cok) *reinterpret_cast<uint4*>(ob) = odd ? mine1 : got;
                         }
                     }
                 }
