@@ -386,13 +386,24 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         if (g.pool_input)
             tc::maxpool_nhwc(T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
                              T.tw.pool.as<bf16>() + T.tw.pool_off[gi], geo, stream_, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi]);
+        // batch statistics ride in the conv epilogue where one 16-channel block is the whole output (the full-resolution layers):
+        // saves the pass that re-reads z
+        static const bool no_fused_stats = getenv("AB_NO_FUSED_STATS") != nullptr;
+        const bool fused_stats = g.dlib_bn >= 0 && !no_fused_stats && t.fwd.size() == 1 && t.fwd[0].mode == tc::OUT_F32_NHWC &&
+                                 t.fwd[0].nblk == 16 && t.fwd[0].npad_total == 16;
+        if (fused_stats) {
+            k::fill_zero(T.sums.p, sizeof(double) * 2 * g.cout, stream_);
+            t.fwd[0].stat_sums = T.sums.as<double>();
+            t.fwd[0].stat_mish = g.has_mish && !g.bn_first;
+        }
         for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, stream_);
+        if (fused_stats) t.fwd[0].stat_sums = nullptr;   // (the launch took its copy)
         if (g.dlib_bn >= 0) {
             const int mish_first = g.bn_first ? 0 : 1;
             float* stats = t_stats_.as<float>() + stats_off_[gi];
             float* rmean = running_.as<float>() + running_off_[gi];
             const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
-            tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_, down);
+            if (!fused_stats) tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_, down);
             const double m = (double)((long long)n * geo.H * geo.W);
             const float eps = (float)model_.layers[g.dlib_bn].eps;
             if (g.dead) {

@@ -129,6 +129,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_slot;
     __shared__ __align__(16) float s_bias[512], s_scale[512], s_shift[512];
+    __shared__ double s_stat[32];
 
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     const int grid_x = (int)L.grid_x, items = grid_x * (L.npad_total / L.nblk);   // (host checks that positions fit 31 bits)
     const int nbuf = L.nbuf;
 
+    if (threadIdx.x < 32) s_stat[threadIdx.x] = 0.0;
     if (threadIdx.x == 0) {
         for (int s = 0; s < L.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiThreads); }
@@ -250,6 +252,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         const int act = L.act, nblk = L.nblk, P = L.P, rows_per_sample = L.H + 1;
         // position step between this thread's consecutive tiles (kTileStep M tiles), as rows + columns of the [rows][P] array
         const int step_r = (kTileStep * L.m_pos_stride) / P, step_c = (kTileStep * L.m_pos_stride) % P;
+        const bool stats = L.stat_sums != nullptr;   // (host: only with OUT_F32_NHWC and nblk == npad_total == 16)
+        float ssum[16] = {}, ssq[16] = {};
         uint32_t ai = 0;
         for (int it0 = blockIdx.x; it0 < items; it0 += gridDim.x, ++ai) {
             const int item = rev ? items - 1 - it0 : it0;
@@ -352,6 +356,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                                 if (co0 + i < L.cout) o[(long long)(co0 + i) * hw] = v[i];
                         }
                     } else if (L.mode == OUT_F32_NHWC) {
+                        if (stats && valid) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const float x = L.stat_mish ? mish_fast(v[i]) : v[i];
+                                ssum[i] += x;
+                                ssq[i] = fmaf(x, x, ssq[i]);
+                            }
+                        }
                         // row = four 16-byte quarters Q0..Q3; even lane writes Q0, Q2 of both rows, odd lane Q1, Q3
                         float rcv[8];
 #pragma unroll
@@ -419,9 +431,22 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty[buf])) : "memory");
         }
+        if (stats) {   // warp totals -> shared doubles (8 warps) -> one global atomic per channel and CTA below
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                float a = ssum[i], b = ssq[i];
+#pragma unroll
+                for (int o = 16; o; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+                if (lane == 0) { atomicAdd(&s_stat[i], (double)a); atomicAdd(&s_stat[16 + i], (double)b); }
+            }
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (L.stat_sums && threadIdx.x < 32) {
+        const int c = threadIdx.x & 15;
+        if (c < L.cout) atomicAdd(L.stat_sums + (threadIdx.x >> 4) * L.cout + c, s_stat[threadIdx.x]);
+    }
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(L.tmem_cols));
 }
 

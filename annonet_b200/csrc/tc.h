@@ -85,6 +85,10 @@ struct ConvLaunch {
     const float* bias = nullptr;  // [cout] or null
     const float* scale = nullptr; // affine_/bn gamma-like and beta-like per channel (ACT_*)
     const float* shift = nullptr;
+    // fused batch statistics (OUT_F32_NHWC, one N block of 16): stat_sums[c] += sum, stat_sums[cout + c] += sum of squares of the
+    // stored values (of mish(value) with stat_mish) over the valid positions -- what bn_stats_nhwc would re-read z for
+    double* stat_sums = nullptr;
+    int stat_mish = 0;
     long long grid_x = 0;         // CTAs along the positions
     double flops = 0, bytes = 0;  // algorithmic work (for the profiler)
 };
