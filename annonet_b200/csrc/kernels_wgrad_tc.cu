@@ -199,13 +199,14 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(L.tmem_cols));
 }
 
-// out[y*sy + x*sx + tapmap[t]] = sum over splits of scratch[split][tile][t][y][x];  block = 32 outputs x 8 split lanes
-__global__ void __launch_bounds__(256) wgrad_tc_reduce_kernel(const float* __restrict__ scratch, int nsplit, int cxtiles, int ntaps, int cy, int cx,
-                                                              float* __restrict__ out, long long sy, long long sx, int t0, int t1, int t2,
-                                                              int t3, int t4, int t5, int t6, int t7, int t8)
+// out[y*sy + x*sx + tapmap[t]] = sum over splits of scratch[split][tile][t][y][x];  block = 32 outputs x kRL split lanes
+template <int kRL>
+__global__ void __launch_bounds__(32 * kRL) wgrad_tc_reduce_kernel(const float* __restrict__ scratch, int nsplit, int cxtiles, int ntaps, int cy, int cx,
+                                                                   float* __restrict__ out, long long sy, long long sx, int t0, int t1, int t2,
+                                                                   int t3, int t4, int t5, int t6, int t7, int t8)
 {
     const int tapmap[9] = {t0, t1, t2, t3, t4, t5, t6, t7, t8};
-    __shared__ float sh[8][33];
+    __shared__ float sh[kRL][33];
     const int ox = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const long long total = (long long)ntaps * cy * cx;
     const long long i = (long long)blockIdx.x * 32 + ox;
@@ -218,15 +219,15 @@ __global__ void __launch_bounds__(256) wgrad_tc_reduce_kernel(const float* __res
         const int cxt = xg >> 6, x = xg & 63;
         const float* p = scratch + ((size_t)cxt * ntaps + t) * 4096 + y * 64 + x;
         const size_t stride = (size_t)cxtiles * ntaps * 4096;
-#pragma unroll 4
-        for (int sp = sl; sp < nsplit; sp += 8) s += p[sp * stride];
+#pragma unroll 5
+        for (int sp = sl; sp < nsplit; sp += kRL) s += p[sp * stride];
     }
     sh[sl][ox] = s;
     __syncthreads();
     if (sl == 0 && i < total) {
         float r = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) r += sh[k][ox];
+        for (int k = 0; k < kRL; ++k) r += sh[k][ox];
         out[y * sy + xg * sx + tapmap[t]] = r;
     }
 }
@@ -347,9 +348,11 @@ void launch_wgrad_tc(const WgradTcLaunch& L, cudaStream_t st)
     k::ProfScope ps(k::F_WGRAD_TC, L.flops, L.bytes, st);
     wgrad_tc_kernel<<<dim3(L.nsplit, L.cxtiles), kWThreads, L.smem_bytes, st>>>(L);
     const long long total = (long long)L.ntaps * L.cy_real * L.cx_real;
-    wgrad_tc_reduce_kernel<<<(unsigned)((total + 31) / 32), 256, 0, st>>>(L.scratch, L.nsplit, L.cxtiles, L.ntaps, L.cy_real, L.cx_real, L.out,
-                                                                         L.sy, L.sx, L.tapmap[0], L.tapmap[1], L.tapmap[2], L.tapmap[3],
-                                                                         L.tapmap[4], L.tapmap[5], L.tapmap[6], L.tapmap[7], L.tapmap[8]);
+    static const int rl = getenv("AB_RL") ? atoi(getenv("AB_RL")) : 4;   // split lanes per 32 outputs: 4 measured best (2: 7.88, 4: 7.85, 8: 7.88, 16: 7.98, 32: 8.47 ms per step)
+#define AB_REDUCE(R) wgrad_tc_reduce_kernel<R><<<(unsigned)((total + 31) / 32), 32 * R, 0, st>>>(L.scratch, L.nsplit, L.cxtiles, L.ntaps, L.cy_real, L.cx_real, L.out, \
+        L.sy, L.sx, L.tapmap[0], L.tapmap[1], L.tapmap[2], L.tapmap[3], L.tapmap[4], L.tapmap[5], L.tapmap[6], L.tapmap[7], L.tapmap[8])
+    if (rl == 2) AB_REDUCE(2); else if (rl == 16) AB_REDUCE(16); else if (rl == 8) AB_REDUCE(8); else AB_REDUCE(4);
+#undef AB_REDUCE
     k::count_launch(2);
 }
 
