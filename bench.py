@@ -323,6 +323,11 @@ def own_arm(args):
             traffic, traffic_src = ent["dram_bytes_per_launch"], tj.get("source")
     except (OSError, ValueError, KeyError):
         pass
+    if tensor_bound and top["bytes"]:
+        # the full-resolution layers of this net (8..64 channels) sit below the bf16 ridge (~215 FLOP/B): the same launches against HBM
+        gbs = top["bytes"] / (top["ms"] * 1e-3) / 1e9
+        roof["hbm_view"] = {"achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                            "note": "algorithmic bytes (operands read once, result written once) / launch time"}
     roof.update({"traffic": traffic, "traffic_source": traffic_src, "kernel": top["name"], "avg_launch_ms": avg_ms, "share_of_step": top["ms"] / total_ms,
                  "peak_source": pk["source"] + (" (sustained bf16 cuBLAS)" if tensor_bound else " (copy)")})
     families = {f["name"]: {"launches_per_step": f["launches"] / args.steps, "ms_per_step": f["ms"] / args.steps,
