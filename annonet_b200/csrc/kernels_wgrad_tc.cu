@@ -254,15 +254,18 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     int grid3[3][3];
     for (auto& r : grid3) for (int& v : r) v = -1;
     bool full3 = job.ntaps == 9 && L.N == 16 && !no_shift;
+    int dy0 = 1 << 30, dx0 = 1 << 30;   // corner of the 3 x 3 stencil (-1, -1 for con_, -2, -2 for the zero-stuffed cont_)
+    for (int t = 0; t < job.ntaps; ++t) { dy0 = std::min(dy0, job.tap_dy[t]); dx0 = std::min(dx0, job.tap_dx[t]); }
     for (int t = 0; t < job.ntaps && full3; ++t) {
-        if (std::abs(job.tap_dy[t]) > 1 || std::abs(job.tap_dx[t]) > 1 || grid3[job.tap_dy[t] + 1][job.tap_dx[t] + 1] >= 0) full3 = false;
-        else grid3[job.tap_dy[t] + 1][job.tap_dx[t] + 1] = t;
+        const int a = job.tap_dy[t] - dy0, b = job.tap_dx[t] - dx0;
+        if (a > 2 || b > 2 || grid3[a][b] >= 0) full3 = false;
+        else grid3[a][b] = t;
     }
     int ntaps = job.ntaps, tdy[9], tdx[9];
     for (int t = 0; t < job.ntaps; ++t) { tdy[t] = job.tap_dy[t]; tdx[t] = job.tap_dx[t]; }
-    if (full3) {
+    if (full3) {   // A sees (dy, dx_max) only; shift s of DY turns it into dx_max - s
         ntaps = 3;
-        for (int t = 0; t < 3; ++t) { tdy[t] = t - 1; tdx[t] = 1; }
+        for (int t = 0; t < 3; ++t) { tdy[t] = dy0 + t; tdx[t] = dx0 + 2; }
     }
     int dylo = 0, dyhi = 0, dxlo = 0, dxhi = 0;
     for (int t = 0; t < ntaps; ++t) {
@@ -313,11 +316,11 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
         L.pair_seg[a] = tdy[t1] - dylo; L.pair_off[a] = tdx[t1] - dxlo;
         L.pair_lbo[a] = t2 >= 0 ? (key[t2] - key[t1]) * 128 : 1024;
         if (L.pair_lbo[a] <= 0 || L.pair_lbo[a] >= (1 << 18)) throw std::logic_error("wgrad_tc: tap pair distance out of range");
-        if (full3)   // position p of DY at shift s pairs with X[p - s + dy*P + 1]: dx = 1 - s
+        if (full3)   // position p of DY at shift s pairs with X[p - s + dy*P + dx_max]: dx = dx_max - s
             for (int h = 0; h < 2; ++h)
                 for (int sft = 0; sft < 3; ++sft) {
                     const int ts = h ? t2 : t1;
-                    L.sh_tap[a][h][sft] = ts >= 0 ? grid3[tdy[ts] + 1][(1 - sft) + 1] : -1;
+                    L.sh_tap[a][h][sft] = ts >= 0 ? grid3[tdy[ts] - dy0][2 - sft] : -1;
                 }
     }
     L.shift = full3 ? 1 : 0;
