@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
 
     if (warp == 0) {
         if (elect_one()) {
-            const uint32_t tx = L.x_stage_bytes + (uint32_t)L.th * (L.shift ? (uint32_t)(L.kw + 8) * 32u : (uint32_t)L.kw * 128u);
+            const uint32_t tx = L.x_stage_bytes + (uint32_t)L.th * (L.shift ? (uint32_t)(L.kw + 8) * (uint32_t)(2 * L.N) : (uint32_t)L.kw * 128u);
             uint32_t it = 0;
             for (long long chunk = c_begin; chunk < c_end; ++chunk, ++it) {
                 const int s = it % L.stages;
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 for (int sg = 0; sg < L.nseg; ++sg)
                     tma_2d(xs + (uint32_t)(sg * L.seg_alloc) * 128u, &L.tmX, L.x_c0 + cxt * 64, o0 + L.seg_pos[sg], &full_bar[s]);
                 for (int m = 0; m < L.th; ++m) {
-                    if (L.shift) tma_2d(ys + (uint32_t)(m * (L.kw + 8)) * 32u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
+                    if (L.shift) tma_2d(ys + (uint32_t)(m * (L.kw + 8)) * (uint32_t)(2 * L.N), &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
                     else tma_2d(ys + (uint32_t)(m * L.kw) * 128u, &L.tmY, L.dy_c0, o0 + m * L.run_stride, &full_bar[s]);
                 }
             }
@@ -143,7 +143,9 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
             // descriptor high word: SBO = 1024 bytes (8 positions), version 1, 128-byte swizzle
             const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
             // B in shift mode: SBO = 256 bytes (8 positions of 32 bytes), 32-byte swizzle
-            const uint32_t b_hi = L.shift ? (256u >> 4) | (1u << 14) | (6u << 29) : desc_hi;
+            // (N = 16: 32-byte rows and swizzle, layout type 6;  N = 32: 64-byte rows and swizzle, layout type 4;  SBO = 8 rows)
+            const uint32_t b_hi = L.shift ? ((uint32_t)(16 * L.N) >> 4) | (1u << 14) | ((L.N == 16 ? 6u : 4u) << 29) : desc_hi;
+            const uint32_t row16 = (uint32_t)(2 * L.N) >> 4;   // shift mode: 16-byte units per staged DY row
             const int ksteps = L.kw / 16, npairs = L.npairs;
             uint32_t pa_off[5], pa_lbo[5];
             for (int a = 0; a < 5; ++a) {
@@ -158,9 +160,9 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 const uint32_t xs16 = (smem0 + (uint32_t)s * L.stage_bytes) >> 4, ys16 = xs16 + (L.x_stage_bytes >> 4);
                 for (int m = 0; m < L.th; ++m)
                     for (int kk = 0; kk < ksteps; ++kk) {
-                        // shift mode: three 16-channel atoms (one per shift) ONE ROW apart (LBO = 32 bytes) in the same staged tile;
+                        // shift mode: three N-channel atoms (one per shift) ONE ROW apart (LBO = one row) in the same staged tile;
                         // the swizzle works on absolute shared-memory addresses, so a row offset keeps matching what TMA wrote
-                        const uint32_t b_lo = L.shift ? (ys16 + (uint32_t)(m * (L.kw + 8) + kk * 16) * 2u) | (2u << 16)
+                        const uint32_t b_lo = L.shift ? (ys16 + (uint32_t)(m * (L.kw + 8) + kk * 16) * row16) | (row16 << 16)
                                                       : (ys16 + (uint32_t)(m * L.kw + kk * 16) * 8u) | (1u << 16);
                         const uint32_t a_base = xs16 + (uint32_t)(m * L.seg_alloc + kk * 16) * 8u;
                         const uint32_t acc = (uint32_t)(it | m | kk);
@@ -185,9 +187,9 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
                 float v[16];
                 tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * L.Nmma + j), v);
                 // shift mode: column block j / 16 is the dx tap of this row half's dy; else 16 more DY channels of `tap`
-                const int tp = L.shift ? L.sh_tap[a][q >> 1][j >> 4] : tap;
+                const int tp = L.shift ? L.sh_tap[a][q >> 1][j / L.N] : tap;
                 if (tp >= 0) {
-                    float* o = sc + (size_t)tp * 4096 + (size_t)(L.shift ? 0 : j) * 64 + x;
+                    float* o = sc + (size_t)tp * 4096 + (size_t)(L.shift ? j % L.N : j) * 64 + x;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) o[i * 64] = v[i];
                 }
@@ -253,7 +255,7 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     static const bool no_shift = getenv("AB_WGRAD_NOSHIFT") != nullptr;
     int grid3[3][3];
     for (auto& r : grid3) for (int& v : r) v = -1;
-    bool full3 = job.ntaps == 9 && L.N == 16 && !no_shift;
+    bool full3 = job.ntaps == 9 && (L.N == 16 || L.N == 32) && !no_shift;
     int dy0 = 1 << 30, dx0 = 1 << 30;   // corner of the 3 x 3 stencil (-1, -1 for con_, -2, -2 for the zero-stuffed cont_)
     for (int t = 0; t < job.ntaps; ++t) { dy0 = std::min(dy0, job.tap_dy[t]); dx0 = std::min(dx0, job.tap_dx[t]); }
     for (int t = 0; t < job.ntaps && full3; ++t) {
@@ -281,7 +283,7 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     double best = 1e300;
     auto consider = [&](int rows_mode, int kw, int th) {
         const int nseg = th + dyr, seg_alloc = (kw + dxr + 7) / 8 * 8;
-        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = (xb + (size_t)th * (full3 ? (kw + 8) * 32 : kw * 128) + 1023) / 1024 * 1024;
+        const size_t xb = (size_t)nseg * seg_alloc * 128, sb = (xb + (size_t)th * (full3 ? (kw + 8) * 2 * L.N : kw * 128) + 1023) / 1024 * 1024;
         if (nseg > 12 || seg_alloc > 256 || 2 * sb + 1024 > budget) return;
         const int stages = (int)std::min<size_t>(kWMaxStages, (budget - 1024) / sb);
         const double score = (double)(nseg * seg_alloc + th * (full3 ? kw + 8 : kw)) / (th * kw) * (stages >= 3 ? 1.0 : 1.15);
@@ -324,7 +326,7 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
                 }
     }
     L.shift = full3 ? 1 : 0;
-    L.Nmma = full3 ? 48 : L.N;
+    L.Nmma = full3 ? 3 * L.N : L.N;
     int cols = 32;
     while (cols < L.npairs * L.Nmma) cols *= 2;
     L.tmem_cols = cols;
@@ -335,7 +337,7 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     L.cy_real = job.cy_real ? job.cy_real : job.cy; L.cx_real = job.cx_real ? job.cx_real : job.cx;
     make_tensor_map_2d(&L.tmX, job.x, job.g.positions(), job.x_ctot, 64, L.seg_alloc);
     // shift mode: one [kw + 8][16] tile per run (32-byte rows, 32-byte swizzle); the three shifts are row offsets into it
-    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, L.shift ? 16 : 64, L.shift ? L.kw + 8 : L.kw);
+    make_tensor_map_2d(&L.tmY, job.dy, job.g.positions(), job.dy_ctot, L.shift ? L.N : 64, L.shift ? L.kw + 8 : L.kw);
     const double px = (double)job.g.N * job.g.H * job.g.W;
     L.flops = 2.0 * px * L.cx_real * L.cy_real * job.ntaps;
     L.bytes = 2.0 * px * (job.cx + job.cy);
