@@ -10,6 +10,10 @@
 //   * A tap shift is a row offset into the staged halo segment (as in the forward kernel); TWO taps share one M = 128
 //     MMA: rows 0-63 are the 64 X channels at tap t1, rows 64-127 the same channels at tap t2, reached through
 //     LBO = (offset(t2) - offset(t1)) * 128 bytes.  Nine taps = five MMAs per 16 positions.
+//   * Shift mode (3x3 stencils, <= 32 DY channels): the three dx taps ride on B instead.  DY is staged once per run as a
+//     [kw + 8][16 | 32] tile (32- or 64-byte rows, matching swizzle); its N = 48 | 96 operand is three atoms ONE ROW apart
+//     (LBO = one row: shift s reads DY[p + s]), against X at (dy, dx_max): G[dy][dx_max - s] for s = 0, 1, 2 from one MMA,
+//     two MMAs (dy pair + single dy) per 16 positions instead of five.
 //   * A CTA owns one 64-channel tile of X, all taps, and a contiguous range of position chunks (split-K); partial sums
 //     leave TMEM once, at the end, to scratch[split][tile][tap][y][x]; wgrad_tc_reduce adds the splits and scatters
 //     into the gradient arena in dlib's filter layout.
