@@ -17,9 +17,9 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libannonet_b200.so")
 
-AB_PRECISION_FP32, AB_PRECISION_BF16 = 0, 1
+AB_PRECISION_FP32, AB_PRECISION_F16 = 0, 1
 (HYPER_LEARNING_RATE, HYPER_WEIGHT_DECAY, HYPER_MOMENTUM, HYPER_BN_STATS_WINDOW, HYPER_LR_SHRINK_FACTOR,
- HYPER_ITERS_WITHOUT_PROGRESS, HYPER_SOLVER, HYPER_ADAM_BETA1, HYPER_ADAM_BETA2, HYPER_SKIP_DEAD_LAYERS) = range(10)
+ HYPER_ITERS_WITHOUT_PROGRESS, HYPER_SOLVER, HYPER_ADAM_BETA1, HYPER_ADAM_BETA2, HYPER_SKIP_DEAD_LAYERS, HYPER_LOSS_SCALE) = range(11)
 
 WLABEL = np.dtype([("label", "<u2"), ("weight", "<f4")], align=True)  # == ab_wlabel, 8 bytes
 assert WLABEL.itemsize == 8
@@ -280,6 +280,8 @@ class TrainingNet(_Net):
 
     def _set(self, hid: int, v: float) -> None:
         _check(lib.ab_set_hyper(self._h, hid, C.c_double(v)))
+
+    set_hyper = _set
 
     def SetLearningRate(self, lr: float) -> None:
         self._set(HYPER_LEARNING_RATE, lr)

@@ -53,7 +53,7 @@ ab_status ab_net_create(int device, int precision, ab_net** out)
 {
     return guarded([&] {
         if (!out) throw std::invalid_argument("null out");
-        if (precision != AB_PRECISION_FP32 && precision != AB_PRECISION_BF16) throw std::invalid_argument("unknown precision");
+        if (precision != AB_PRECISION_FP32 && precision != AB_PRECISION_F16) throw std::invalid_argument("unknown precision");
         auto n = std::make_unique<ab_net>();
         n->eng = std::make_unique<ab::Engine>(device, precision);
         *out = n.release();
@@ -213,6 +213,7 @@ ab_status ab_set_hyper(ab_net* net, int id, double v)
         case AB_HYPER_ADAM_BETA1: e.hyper.adam_beta1 = v; break;
         case AB_HYPER_ADAM_BETA2: e.hyper.adam_beta2 = v; break;
         case AB_HYPER_SKIP_DEAD_LAYERS: e.hyper.skip_dead_layers = (int)v; break;
+        case AB_HYPER_LOSS_SCALE: e.hyper.loss_scale = v; break;
         default: throw std::invalid_argument("unknown hyper-parameter id");
         }
     });
@@ -232,6 +233,7 @@ ab_status ab_get_hyper(ab_net* net, int id, double* v)
         case AB_HYPER_ADAM_BETA1: *v = e.hyper.adam_beta1; break;
         case AB_HYPER_ADAM_BETA2: *v = e.hyper.adam_beta2; break;
         case AB_HYPER_SKIP_DEAD_LAYERS: *v = e.hyper.skip_dead_layers; break;
+        case AB_HYPER_LOSS_SCALE: *v = e.hyper.loss_scale; break;
         default: throw std::invalid_argument("unknown hyper-parameter id");
         }
     });

@@ -44,10 +44,11 @@ struct Hyper {
     int solver = 0;                // 0 sgd, 1 adam
     double adam_beta1 = 0.9, adam_beta2 = 0.999;
     int skip_dead_layers = 0;
+    double loss_scale = 0;         // fp16 path: 0 = automatic (a power of two near n*h*w/4)
 };
 
 struct NcclApi;
-struct TcState;  // bf16 tensor-core path: workspaces, packed filters, launch descriptors (engine_bf16.cu)
+struct TcState;  // h16 tensor-core path: workspaces, packed filters, launch descriptors (engine_bf16.cu)
 
 class Engine {
 public:
@@ -105,7 +106,7 @@ private:
     void optimizer_step();
     void allreduce_range(size_t lo, size_t hi);
     k::Slice level_slice(Levels& L, int level, int c0, int C) const;
-    // bf16 tensor-core path (precision_ == AB_PRECISION_BF16)
+    // h16 tensor-core path (precision_ == AB_PRECISION_F16)
     void tc_ensure_infer(int h, int w);
     void tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w);
     void tc_run_inference(int h, int w);

@@ -125,7 +125,7 @@ void Engine::load(const NetModel& m)
     synchronize();
     model_ = m;
     plan_ = build_plan(model_);
-    tc_.reset();  // filter packs and launch descriptors of the bf16 path belong to the old parameters
+    tc_.reset();  // filter packs and launch descriptors of the h16 path belong to the old parameters
     const size_t np = plan_.num_params;
     std::vector<float> hp(np, 0.f), lrm(np, 1.f), wdm(np, 1.f);
     running_off_.assign(plan_.groups.size(), 0);

@@ -63,7 +63,7 @@ const float* Engine::forward_device(const uint8_t* img_dev, int h, int w)
 {
     if (!loaded_) throw state_error("no net loaded");
     AB_CUDA(cudaSetDevice(device_));
-    if (precision_ == 1) {  // AB_PRECISION_BF16: tcgen05 path
+    if (precision_ == 1) {  // AB_PRECISION_F16: tcgen05 path
         tc_input(img_dev, h, w, 0, 0, h, w);
         tc_run_inference(h, w);
         return i_logits_.as<float>();

@@ -1,5 +1,5 @@
-// bf16 tensor-core path of the engine (AB_PRECISION_BF16): the same conv groups as the fp32 path
-// (plan.h), executed as tcgen05 implicit GEMMs over padded flat NHWC bf16 tensors (tc.h).
+// fp16 tensor-core path of the engine (AB_PRECISION_F16): the same conv groups as the fp32 path
+// (plan.h), executed as tcgen05 implicit GEMMs over padded flat NHWC fp16 tensors (tc.h).
 #include "engine.h"
 #include "tc_state.h"
 
@@ -7,7 +7,7 @@
 
 namespace ab {
 
-using tc::bf16;
+using tc::h16;
 using tc::ConvLaunch;
 using tc::ConvSetup;
 using tc::Geo;
@@ -59,7 +59,7 @@ void forward_taps(const ConvGroup& g, TcGroup& t)
 
 }  // namespace
 
-// (re)build the bf16 filter packs of the forward direction from the fp32 parameter arena
+// (re)build the h16 filter packs of the forward direction from the fp32 parameter arena
 void Engine::tc_pack_forward_filters()
 {
     if (!tc_) tc_ = std::make_unique<TcState>();
@@ -78,7 +78,7 @@ void Engine::tc_pack_forward_filters()
                 off += (tc::packed_filter_elems(cin, t.npad, t.fwd_ntaps[l]) + 511) / 512 * 512;  // keep 1 KB alignment
             }
         }
-        T.fwd_packs.reserve(off * sizeof(bf16));
+        T.fwd_packs.reserve(off * sizeof(h16));
         T.fwd_packs_valid = false;
     }
     if (T.fwd_packs_valid) return;
@@ -90,7 +90,7 @@ void Engine::tc_pack_forward_filters()
         // arena: con_ [cout][cin][kk], cont_ [cin][cout][kk]
         const long long sn = g.is_cont ? kk : (long long)g.cin * kk, sk = g.is_cont ? (long long)g.cout * kk : kk;
         for (int l = 0; l < t.nlaunch; ++l)
-            tc::pack_filters_bf16(P + g.w_off, T.fwd_packs.as<bf16>() + t.fwd_pack_off[l], g.cout, t.npad, g.cin, t.fwd_ntaps[l],
+            tc::pack_filters_bf16(P + g.w_off, T.fwd_packs.as<h16>() + t.fwd_pack_off[l], g.cout, t.npad, g.cin, t.fwd_ntaps[l],
                                   t.fwd_tapmap[l], sn, sk, stream_);
     }
     AB_CUDA(cudaGetLastError());
@@ -98,20 +98,23 @@ void Engine::tc_pack_forward_filters()
 }
 
 // workspace of padded flat NHWC level buffers for n samples of h x w
-void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, cudaStream_t st)
+void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, bool split, cudaStream_t st)
 {
-    if (ws.n == n && ws.h == h && ws.w == w) return;
+    if (ws.n == n && ws.h == h && ws.w == w && ws.split == split) return;
     const LevelDims d = level_dims(h, w, plan.levels);
+    const size_t halves = split ? 2 : 1;
     for (int l = 0; l <= plan.levels; ++l) {
         ws.geo[l].N = n; ws.geo[l].H = d.h[l]; ws.geo[l].W = d.w[l];
-        const size_t bytes = (size_t)ws.geo[l].positions() * plan.level_channels[l] * sizeof(bf16);
-        ws.level[l].reserve(bytes);
-        AB_CUDA(cudaMemsetAsync(ws.level[l].p, 0, bytes, st));  // pad positions must be zero and stay zero
+        const size_t elems = (size_t)ws.geo[l].positions() * plan.level_channels[l];
+        ws.level_lo[l] = split ? (long long)elems : 0;
+        ws.level[l].reserve(elems * halves * sizeof(h16));
+        AB_CUDA(cudaMemsetAsync(ws.level[l].p, 0, elems * halves * sizeof(h16), st));  // pad positions must be zero and stay zero
     }
     if (with_image) {
-        const size_t bytes = (size_t)ws.geo[0].positions() * 8 * sizeof(bf16);
-        ws.img.reserve(bytes);
-        AB_CUDA(cudaMemsetAsync(ws.img.p, 0, bytes, st));
+        const size_t elems = (size_t)ws.geo[0].positions() * 8;
+        ws.img_lo = split ? (long long)elems : 0;
+        ws.img.reserve(elems * halves * sizeof(h16));
+        AB_CUDA(cudaMemsetAsync(ws.img.p, 0, elems * halves * sizeof(h16), st));
     }
     if (with_pool) {
         ws.pool_off.assign(plan.groups.size(), 0);
@@ -120,18 +123,20 @@ void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bo
             const ConvGroup& g = plan.groups[gi];
             if (!g.pool_input) continue;
             ws.pool_off[gi] = off;
-            off += ((size_t)ws.geo[g.out_level].positions() * g.cin + 63) / 64 * 64;
+            // split: the group's lo half follows its hi half directly (positions * cin elements behind)
+            off += ((size_t)ws.geo[g.out_level].positions() * g.cin * halves + 63) / 64 * 64;
         }
-        ws.pool.reserve(off * sizeof(bf16));
-        AB_CUDA(cudaMemsetAsync(ws.pool.p, 0, off * sizeof(bf16), st));
+        ws.pool.reserve(off * sizeof(h16));
+        AB_CUDA(cudaMemsetAsync(ws.pool.p, 0, off * sizeof(h16), st));
     }
-    ws.n = n; ws.h = h; ws.w = w;
+    ws.n = n; ws.h = h; ws.w = w; ws.split = split;
 }
 
 // prepared launch of one conv group in the forward direction.  `dst`/`dst_ctot`/`dst_c0`: where the result goes
 // (a level slice, a dense z tensor, or the f32 logits planes), `mode`/`act` as in tc.h.
-void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const bf16* packs,
-                                   const float* P, std::vector<ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0, int mode, int act)
+void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const h16* packs,
+                            const size_t* pack_off, const float* P, std::vector<ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0,
+                            long long dst_lo_off, int mode, int act)
 {
     out.assign(t.nlaunch, ConvLaunch());
     const bool up = g.is_cont && g.stride == 2;
@@ -140,11 +145,13 @@ void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup&
     const Geo& grid = up ? ws.geo[g.in_level] : ws.geo[ol];
     for (int l = 0; l < t.nlaunch; ++l) {
         ConvSetup s;
-        if (g.in_level < 0) { s.src = ws.img.as<bf16>(); s.src_ctot = 8; s.a_c0 = 0; s.cin = 8; }
-        else if (g.pool_input) { s.src = ws.pool.as<bf16>() + ws.pool_off[&g - plan.groups.data()]; s.src_ctot = g.cin; s.a_c0 = 0; s.cin = g.cin; }
-        else { s.src = ws.level[g.in_level].as<bf16>(); s.src_ctot = plan.level_channels[g.in_level]; s.a_c0 = g.in_c0; s.cin = g.cin; }
+        if (g.in_level < 0) { s.src = ws.img.as<h16>(); s.src_ctot = 8; s.a_c0 = 0; s.cin = 8; }
+        else if (g.pool_input) { s.src = ws.pool.as<h16>() + ws.pool_off[&g - plan.groups.data()]; s.src_ctot = g.cin; s.a_c0 = 0; s.cin = g.cin; }
+        else { s.src = ws.level[g.in_level].as<h16>(); s.src_ctot = plan.level_channels[g.in_level]; s.a_c0 = g.in_c0; s.cin = g.cin; }
         s.src_positions = grid.positions();
-        s.packed = packs + t.fwd_pack_off[l];
+        // split workspace: the lo halves sit exactly src_positions rows behind the hi halves (one tensor map covers both)
+        s.split = ws.split ? 1 : 0;
+        s.packed = packs + pack_off[l];
         s.ntaps = t.fwd_ntaps[l];
         for (int i = 0; i < s.ntaps; ++i) { s.tap_dy[i] = t.fwd_tapdy[l][i]; s.tap_dx[i] = t.fwd_tapdx[l][i]; }
         s.npad_total = t.npad;
@@ -153,7 +160,7 @@ void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup&
         tc::setup_conv(L, s);
         L.mode = mode; L.act = act;
         L.cout = g.cout;
-        L.out = dst; L.out_ctot = dst_ctot; L.out_c0 = dst_c0;
+        L.out = dst; L.out_ctot = dst_ctot; L.out_c0 = dst_c0; L.out_lo_off = dst_lo_off;
         L.bias = P + g.b_off;
         if (act != tc::ACT_NONE) { L.scale = P + g.bn_off; L.shift = P + g.bn_off + g.cout; }
         if (up) {
@@ -161,9 +168,12 @@ void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup&
             L.par_a = l / 2; L.par_b = l % 2;
             L.out_S = ws.geo[ol].S(); L.out_P = ws.geo[ol].P();
         }
+        // algorithmic work: the convolution's FLOPs (the three MMAs of a split chunk are an implementation cost, not work) and one
+        // read of the input + one write of the output in their stored widths
         const double px = (double)grid.N * grid.H * grid.W;
         L.flops = 2.0 * px * g.cin * g.cout * s.ntaps;
-        L.bytes = 2.0 * px * (g.cin + g.cout) / (up ? 1.0 : 1.0);
+        const double out_b = (mode == tc::OUT_F32_NHWC || mode == tc::OUT_F32_NCHW) ? 4.0 : (dst_lo_off ? 4.0 : 2.0);
+        L.bytes = px * ((ws.split ? 4.0 : 2.0) * g.cin + out_b * g.cout * (up ? 1.0 : 1.0));
     }
 }
 
@@ -172,7 +182,7 @@ void Engine::tc_ensure_infer(int h, int w)
     tc_pack_forward_filters();
     TcState& T = *tc_;
     if (T.iw.h == h && T.iw.w == w && T.iw.n == 1) return;
-    ensure_workspace(T.iw, plan_, 1, h, w, true, true, stream_);
+    ensure_workspace(T.iw, plan_, 1, h, w, true, true, false, stream_);
     i_logits_.reserve((size_t)plan_.class_count * h * w * sizeof(float));
     const float* P = params_.as<float>();
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
@@ -183,17 +193,17 @@ void Engine::tc_ensure_infer(int h, int w)
         int act = tc::ACT_NONE;
         if (g.dlib_bn >= 0) act = g.bn_first ? tc::ACT_AFFINE_MISH : tc::ACT_MISH_AFFINE;
         if (g.out_level == -2)
-            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<bf16>(), P, t.infer, i_logits_.p, 0, 0, tc::OUT_F32_NCHW, act);
+            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<h16>(), t.fwd_pack_off, P, t.infer, i_logits_.p, 0, 0, 0, tc::OUT_F32_NCHW, act);
         else
-            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<bf16>(), P, t.infer, T.iw.level[g.out_level].p,
-                                   plan_.level_channels[g.out_level], g.out_c0, tc::OUT_BF16, act);
+            setup_forward_launches(plan_, g, t, T.iw, T.fwd_packs.as<h16>(), t.fwd_pack_off, P, t.infer, T.iw.level[g.out_level].p,
+                                   plan_.level_channels[g.out_level], g.out_c0, 0, tc::OUT_BF16, act);
     }
 }
 
 void Engine::tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w)
 {
     tc_ensure_infer(h, w);
-    tc::image_to_nhwc(img_dev, IH, IW, left, top, tc_->iw.img.as<bf16>(), tc_->iw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+    tc::image_to_nhwc(img_dev, IH, IW, left, top, tc_->iw.img.as<h16>(), tc_->iw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
 }
 
 void Engine::tc_run_inference(int h, int w)
@@ -204,8 +214,8 @@ void Engine::tc_run_inference(int h, int w)
         const ConvGroup& g = plan_.groups[gi];
         if (g.dead) continue;
         if (g.pool_input)
-            tc::maxpool_nhwc(T.iw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.iw.geo[g.in_level],
-                             T.iw.pool.as<bf16>() + T.iw.pool_off[gi], T.iw.geo[g.out_level], stream_);
+            tc::maxpool_nhwc(T.iw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.iw.geo[g.in_level],
+                             T.iw.pool.as<h16>() + T.iw.pool_off[gi], T.iw.geo[g.out_level], stream_);
         for (const ConvLaunch& L : T.groups[gi].infer) tc::launch_conv(L, stream_);
     }
     AB_CUDA(cudaGetLastError());

@@ -1,11 +1,12 @@
-// Training step of the bf16 tensor-core path (AB_PRECISION_BF16): the dnn_trainer step of engine_train.cu
-// (trainer.h:631-671,743-828) over padded flat NHWC bf16 tensors (tc.h).
-//   forward : conv (tcgen05, kernels_tc.cu) -> z [fp32] -> batch statistics -> bn/mish -> level slice
-//   loss    : fp32 logits planes (the head conv writes them directly) -> loss + gradient (kernels_misc.cu)
-//   backward: bn/mish backward (z, gy -> dz [bf16], + bias gradient) -> filter gradient (kernels_wgrad_mma.cu)
-//             -> backward-data as a tcgen05 conv with transposed filters accumulating into the gradient level slice
-//   update  : fp32 master parameters / fp32 gradient arena, the same fused SGD/Adam kernel as the fp32 path;
-//             the bf16 filter packs of both directions are rebuilt from the master copy by one batched kernel.
+// Training step of the fp16 tensor-core path (AB_PRECISION_F16): the dnn_trainer step of engine_train.cu
+// (trainer.h:631-671,743-828) over padded flat NHWC fp16 tensors (tc.h).
+//   forward : conv (tcgen05, kernels_tc.cu; split operands: activations and filters as fp16 hi + lo pairs, three MMAs per
+//             K chunk) -> z [fp32] -> batch statistics -> bn/mish -> level slice [hi | lo]
+//   loss    : fp32 logits planes (the head conv writes them directly) -> loss + gradient (kernels_misc.cu), times the loss scale
+//   backward: bn/mish backward (z, gy -> dz [fp16], + bias gradient) -> filter gradient (kernels_wgrad_tc.cu, hi halves of
+//             the activations) -> backward-data as a tcgen05 conv with transposed filters accumulating into the gradient slice
+//   update  : fp32 master parameters / fp32 gradient arena (unscaled), the same fused SGD/Adam kernel as the fp32 path;
+//             the fp16 filter packs of both directions are rebuilt from the master copy by one batched kernel.
 #include "engine.h"
 #include "kcommon.cuh"
 #include "tc_state.h"
@@ -15,7 +16,7 @@
 
 namespace ab {
 
-using tc::bf16;
+using tc::h16;
 using tc::ConvLaunch;
 using tc::ConvSetup;
 using tc::Geo;
@@ -58,23 +59,30 @@ void Engine::tc_ensure_train(int n, int h, int w)
 {
     if (!tc_) tc_ = std::make_unique<TcState>();
     TcState& T = *tc_;
-    if (T.train_ready && T.tw.n == n && T.tw.h == h && T.tw.w == w) return;
+    // Loss scale: per-pixel gradients are ~1/(n*h*w) times O(1) (loss.h:3158) -- below fp16's normal range.  A power of two near
+    // n*h*w/8 puts them around 2^-3 with ~2^18 of headroom (measured spread over the whole net: 2e-4 .. 2e2 x 1/(n*h*w),
+    // experiments/bf16_emulation.py); conversions saturate instead of overflowing.  hyper.loss_scale overrides.
+    double sc = hyper.loss_scale;
+    if (!(sc > 0)) { sc = 1; while (sc * 8 <= (double)n * h * w) sc *= 2; }
+    if (T.train_ready && T.tw.n == n && T.tw.h == h && T.tw.w == w && T.loss_scale == (float)sc) return;
     synchronize();
+    T.loss_scale = (float)sc;
+    const float unscale = 1.f / T.loss_scale;
     T.train_ready = false;
     // group table + forward pack offsets (shared with the inference path)
     T.fwd_packs_valid = false;
     tc_pack_forward_filters();
     const int K = plan_.class_count;
-    if (K > 8) throw std::invalid_argument("the bf16 training path supports at most 8 classes in this build");
-    ensure_workspace(T.tw, plan_, n, h, w, true, true, stream_);
-    ensure_workspace(T.tg, plan_, n, h, w, false, false, stream_);
+    if (K > 8) throw std::invalid_argument("the tensor-core training path supports at most 8 classes in this build");
+    ensure_workspace(T.tw, plan_, n, h, w, true, true, true, stream_);     // activations: hi + lo halves
+    ensure_workspace(T.tg, plan_, n, h, w, false, false, false, stream_);  // gradients: single fp16 values, loss-scaled
     T.tw.pool_arg.reserve(std::max<size_t>(T.tw.pool.bytes / 2, 256));
     t_logits_.reserve((size_t)n * K * h * w * 4);
     t_glogits_.reserve((size_t)n * K * h * w * 4);
     t_loss_.reserve(sizeof(double));
 
     // per group buffers
-    size_t z_elems = 0, dpool_elems = 0, upx_elems = 0, bwd_elems = 0, stt = 0;
+    size_t z_elems = 0, dpool_elems = 0, upx_elems = 0, bwd_elems = 0, stt = 0, tp_elems = 0;
     int cmax = 8;
     stats_off_.assign(plan_.groups.size(), 0);
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
@@ -82,6 +90,10 @@ void Engine::tc_ensure_train(int n, int h, int w)
         TcGroup& t = T.groups[gi];
         const int ol = g.out_level == -2 ? 0 : g.out_level;
         cmax = std::max(cmax, g.cout);
+        for (int l = 0; l < t.nlaunch; ++l) {   // split forward packs [hi | hi | lo]
+            t.train_pack_off[l] = tp_elems;
+            tp_elems += (3 * tc::packed_filter_elems(g.in_level < 0 ? 8 : g.cin, t.npad, t.fwd_ntaps[l]) + 511) / 512 * 512;
+        }
         if (g.dlib_bn >= 0) {
             stats_off_[gi] = stt; stt += 2 * (size_t)g.cout;
             t.z_off = z_elems;
@@ -107,9 +119,10 @@ void Engine::tc_ensure_train(int n, int h, int w)
     zero_reserve(T.upx, upx_elems * 2);
     zero_reserve(T.glogits16, (size_t)T.tw.geo[0].positions() * 8 * 2);
     zero_reserve(T.bwd_packs, bwd_elems * 2);
+    zero_reserve(T.train_packs, tp_elems * 2);
     T.sums.reserve(sizeof(double) * 2 * cmax);
     T.bias_tmp.reserve(sizeof(float) * 256);
-    T.wscratch.reserve(tc::wgrad_mma_scratch_floats() * 4);
+    T.wscratch.reserve(tc::wgrad_tc_scratch_floats() * 4);
     t_stats_.reserve(std::max<size_t>(stt, 1) * 4);
 
     // filter-pack jobs: every forward launch and every backward-data conv, rebuilt from the fp32 arena each step
@@ -121,11 +134,12 @@ void Engine::tc_ensure_train(int n, int h, int w)
         const int kk = g.ksize * g.ksize;
         for (int l = 0; l < t.nlaunch; ++l) {
             tc::PackJob j{};
-            j.w_off = (long long)g.w_off; j.packed_off = (long long)t.fwd_pack_off[l];
+            j.w_off = (long long)g.w_off; j.packed_off = (long long)t.train_pack_off[l];
             j.sn = g.is_cont ? kk : (long long)g.cin * kk; j.sk = g.is_cont ? (long long)g.cout * kk : kk;
             j.nreal = g.cout; j.npad = t.npad; j.kreal = g.cin; j.kp = tc::padded_k(g.in_level < 0 ? 8 : g.cin); j.ntaps = t.fwd_ntaps[l];
+            j.parts = 3;
             for (int i = 0; i < j.ntaps; ++i) j.tapmap[i] = t.fwd_tapmap[l][i];
-            T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp);
+            T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp * 3);
             jobs.push_back(j);
         }
     }
@@ -140,6 +154,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
         // n = ci, k = co:  con_ [co][ci][kk], cont_ [ci][co][kk]
         j.sn = g.is_cont ? (long long)g.cout * kk : kk; j.sk = g.is_cont ? kk : (long long)g.cin * kk;
         j.nreal = g.cin; j.npad = t.bwd_npad; j.kreal = g.cout; j.kp = tc::padded_k(std::max(g.cout, 8)); j.ntaps = t.bwd_ntaps;
+        j.parts = 1;
         for (int i = 0; i < j.ntaps; ++i) j.tapmap[i] = t.bwd_tapmap[i];
         T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp);
         jobs.push_back(j);
@@ -159,21 +174,22 @@ void Engine::tc_ensure_train(int n, int h, int w)
         const bool up = g.is_cont && g.stride == 2;
         float* z = T.z.as<float>() + t.z_off;
         // forward: conv (+ bias) -> z, the logits planes, or (`up`) the destination slice
+        const h16* tp = T.train_packs.as<h16>();
         if (g.dlib_bn >= 0)
-            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, z, g.cout, 0, tc::OUT_F32_NHWC, tc::ACT_NONE);
+            setup_forward_launches(plan_, g, t, T.tw, tp, t.train_pack_off, P, t.fwd, z, g.cout, 0, 0, tc::OUT_F32_NHWC, tc::ACT_NONE);
         else if (g.out_level == -2)
-            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, t_logits_.p, 0, 0, tc::OUT_F32_NCHW, tc::ACT_NONE);
+            setup_forward_launches(plan_, g, t, T.tw, tp, t.train_pack_off, P, t.fwd, t_logits_.p, 0, 0, 0, tc::OUT_F32_NCHW, tc::ACT_NONE);
         else
-            setup_forward_launches(plan_, g, t, T.tw, T.fwd_packs.as<bf16>(), P, t.fwd, T.tw.level[g.out_level].p,
-                                   plan_.level_channels[g.out_level], g.out_c0, tc::OUT_BF16, tc::ACT_NONE);
+            setup_forward_launches(plan_, g, t, T.tw, tp, t.train_pack_off, P, t.fwd, T.tw.level[g.out_level].p,
+                                   plan_.level_channels[g.out_level], g.out_c0, T.tw.level_lo[g.out_level], tc::OUT_BF16, tc::ACT_NONE);
         t.dgrad.clear();
         if (g.dead) continue;
 
         // gradient at the conv output: dz (in z's place), the loss gradient, or the gradient slice itself
-        const bf16* dz; int dz_ctot, dz_c0, dz_c;
-        if (g.dlib_bn >= 0) { dz = T.dz.as<bf16>() + t.z_off; dz_ctot = g.cout; dz_c0 = 0; dz_c = g.cout; }
-        else if (g.out_level == -2) { dz = T.glogits16.as<bf16>(); dz_ctot = 8; dz_c0 = 0; dz_c = 8; }
-        else { dz = T.tg.level[ol].as<bf16>(); dz_ctot = plan_.level_channels[ol]; dz_c0 = g.out_c0; dz_c = g.cout; }
+        const h16* dz; int dz_ctot, dz_c0, dz_c;
+        if (g.dlib_bn >= 0) { dz = T.dz.as<h16>() + t.z_off; dz_ctot = g.cout; dz_c0 = 0; dz_c = g.cout; }
+        else if (g.out_level == -2) { dz = T.glogits16.as<h16>(); dz_ctot = 8; dz_c0 = 0; dz_c = 8; }
+        else { dz = T.tg.level[ol].as<h16>(); dz_ctot = plan_.level_channels[ol]; dz_c0 = g.out_c0; dz_c = g.cout; }
 
         // filter gradient
         tc::WgradJob& wj = t.wgrad;
@@ -181,11 +197,12 @@ void Engine::tc_ensure_train(int n, int h, int w)
         wj.dy = dz; wj.dy_ctot = dz_ctot; wj.dy_c0 = dz_c0; wj.cy = dz_c; wj.cy_real = g.cout;
         wj.g = T.tw.geo[ol];
         wj.out = G + g.w_off;
+        wj.unscale = unscale;
         const int kk = g.ksize * g.ksize;
-        if (g.in_level < 0) { wj.x = T.tw.img.as<bf16>(); wj.x_ctot = 8; wj.x_c0 = 0; wj.cx = 8; }
-        else if (g.pool_input) { wj.x = T.tw.pool.as<bf16>() + T.tw.pool_off[gi]; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
-        else if (up) { wj.x = T.upx.as<bf16>() + t.upx_off; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
-        else { wj.x = T.tw.level[g.in_level].as<bf16>(); wj.x_ctot = plan_.level_channels[g.in_level]; wj.x_c0 = g.in_c0; wj.cx = g.cin; }
+        if (g.in_level < 0) { wj.x = T.tw.img.as<h16>(); wj.x_ctot = 8; wj.x_c0 = 0; wj.cx = 8; }
+        else if (g.pool_input) { wj.x = T.tw.pool.as<h16>() + T.tw.pool_off[gi]; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
+        else if (up) { wj.x = T.upx.as<h16>() + t.upx_off; wj.x_ctot = g.cin; wj.x_c0 = 0; wj.cx = g.cin; }
+        else { wj.x = T.tw.level[g.in_level].as<h16>(); wj.x_ctot = plan_.level_channels[g.in_level]; wj.x_c0 = g.in_c0; wj.cx = g.cin; }
         wj.cx_real = g.cin;
         wj.ntaps = kk;
         if (!g.is_cont) { wj.sy = (long long)g.cin * kk; wj.sx = kk; } else { wj.sy = kk; wj.sx = (long long)g.cout * kk; }
@@ -205,7 +222,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
         if (g.in_level < 0) continue;
         ConvSetup s;
         s.src = dz; s.src_positions = T.tw.geo[ol].positions(); s.src_ctot = dz_ctot; s.a_c0 = dz_c0; s.cin = dz_c;
-        s.packed = T.bwd_packs.as<bf16>() + t.bwd_pack_off;
+        s.packed = T.bwd_packs.as<h16>() + t.bwd_pack_off;
         s.ntaps = t.bwd_ntaps;
         for (int i = 0; i < s.ntaps; ++i) { s.tap_dy[i] = t.bwd_tapdy[i]; s.tap_dx[i] = t.bwd_tapdx[i]; }
         s.npad_total = t.bwd_npad;
@@ -215,7 +232,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
         tc::setup_conv(L, s);
         L.act = tc::ACT_NONE; L.bias = nullptr;
         L.cout = g.cin;
-        if (g.pool_input) { L.mode = tc::OUT_BF16; L.out = T.dpool.as<bf16>() + t.dpool_off; L.out_ctot = g.cin; L.out_c0 = 0; }
+        if (g.pool_input) { L.mode = tc::OUT_BF16; L.out = T.dpool.as<h16>() + t.dpool_off; L.out_ctot = g.cin; L.out_c0 = 0; }
         else {
             L.mode = up ? tc::OUT_BF16_DOWN_ACCUM : tc::OUT_BF16_ACCUM;
             L.out = T.tg.level[g.in_level].p; L.out_ctot = plan_.level_channels[g.in_level]; L.out_c0 = g.in_c0;
@@ -223,7 +240,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
         }
         const double px = (double)s.grid.N * s.grid.H * s.grid.W;
         L.flops = 2.0 * px * g.cin * g.cout * s.ntaps / (up ? 4.0 : 1.0);
-        L.bytes = 2.0 * px * (g.cin + g.cout);
+        L.bytes = 2.0 * px * (g.cin / (up ? 4.0 : 1.0) + g.cout);
     }
     // Gradient slices: the first writer of a channel range in backward order ASSIGNS (no read-modify-write on the epilogue's
     // critical path, no memset of the level), later writers accumulate (dnn/core.h:958-974 zeroes x_grad and lets every
@@ -253,7 +270,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
                 if (!c) T.grad_level_needs_zero[l] = 1;
         // one zeroing now: assigned slices keep their (never written) pad positions at zero from here on
         for (int l = 0; l <= plan_.levels; ++l)
-            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
+            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(h16), stream_);
         static const bool debug = getenv("AB_TC_DEBUG") != nullptr;
         if (debug)
             for (int l = 0; l <= plan_.levels; ++l) fprintf(stderr, "gradient level %d: memset per step %d\n", l, (int)T.grad_level_needs_zero[l]);
@@ -280,10 +297,10 @@ void Engine::level_values(int level, bool gradient, std::vector<float>& out, int
             for (int c = 0; c < C; ++c)
                 for (int y = 0; y < g.H; ++y)
                     for (int x = 0; x < g.W; ++x) {
-                        const uint32_t bits = (uint32_t)raw[(size_t)g.pos(n, y, x) * C + c] << 16;
-                        float f;
-                        std::memcpy(&f, &bits, 4);
-                        out[(((size_t)n * C + c) * g.H + y) * g.W + x] = f;
+                        __half_raw hr;
+                        hr.x = raw[(size_t)g.pos(n, y, x) * C + c];
+                        const float f = __half2float(__half(hr));   // (activations: the hi halves; gradients: loss-scaled)
+                        out[(((size_t)n * C + c) * g.H + y) * g.W + x] = gradient ? f / T.loss_scale : f;
                     }
     } else {
         Levels& L = gradient ? tw_grad_ : tw_act_;
@@ -308,6 +325,7 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
     if (no_graph || k::prof_enabled() || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update, false); return; }
     TcState::GraphKey key;
     key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
+    key.world = world_; key.solver = hyper.solver; key.loss_scale = hyper.loss_scale;
     key.lr = hyper.learning_rate; key.wd = hyper.weight_decay; key.momentum = hyper.momentum; key.window = window_.empty() ? 0 : window_[0];
     if (!(T.graph_segs.size() && T.graph_key == key)) {
         if (!(T.seen_key == key)) {   // first time: run eagerly
@@ -364,13 +382,14 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
     float* G = grads_.as<float>();
     const int K = plan_.class_count;
 
-    // bf16 filter packs of both directions from the fp32 master parameters
+    // h16 filter packs of both directions from the fp32 master parameters
     const tc::PackJob* jobs = T.pack_jobs.as<tc::PackJob>();
-    tc::pack_filters_batched(P, T.fwd_packs.as<bf16>(), jobs, T.n_fwd_jobs, T.max_pack_elems, stream_);
-    tc::pack_filters_batched(P, T.bwd_packs.as<bf16>(), jobs + T.n_fwd_jobs, T.n_pack_jobs - T.n_fwd_jobs, T.max_pack_elems, stream_);
-    T.fwd_packs_valid = true;
+    tc::pack_filters_batched(P, T.train_packs.as<h16>(), jobs, T.n_fwd_jobs, T.max_pack_elems, stream_);
+    tc::pack_filters_batched(P, T.bwd_packs.as<h16>(), jobs + T.n_fwd_jobs, T.n_pack_jobs - T.n_fwd_jobs, T.max_pack_elems, stream_);
+    T.fwd_packs_valid = false;   // (the inference packs no longer match the parameters once the optimizer has run)
+    const float unscale = 1.f / T.loss_scale;
 
-    tc::image_to_nhwc(imgs_dev, h, w, 0, 0, T.tw.img.as<bf16>(), T.tw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+    tc::image_to_nhwc(imgs_dev, h, w, 0, 0, T.tw.img.as<h16>(), T.tw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_, T.tw.img_lo);
 
     // ---- forward (batch-norm training mode)
     // The two reduction passes (bn statistics, bn backward sums) walk the positions downwards: their producers walked upwards, so
@@ -384,8 +403,9 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         const int ol = g.out_level == -2 ? 0 : g.out_level;
         const Geo& geo = T.tw.geo[ol];
         if (g.pool_input)
-            tc::maxpool_nhwc(T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
-                             T.tw.pool.as<bf16>() + T.tw.pool_off[gi], geo, stream_, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi]);
+            tc::maxpool_nhwc(T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
+                             T.tw.pool.as<h16>() + T.tw.pool_off[gi], geo, stream_, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi],
+                             T.tw.level_lo[g.in_level], geo.positions() * g.cin);
         // batch statistics ride in the conv epilogue where one 16-channel block is the whole output (the full-resolution layers):
         // saves the pass that re-reads z
         static const bool no_fused_stats = getenv("AB_NO_FUSED_STATS") != nullptr;
@@ -415,21 +435,21 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
                 fin.sums = T.sums.as<double>(); fin.m = m; fin.eps = (double)eps;
                 fin.num_updates = nu_dev_.as<unsigned long long>() + gi; fin.window = window_[gi];
                 fin.rmean = rmean; fin.rvar = rmean + g.cout; fin.stats_out = stats;
-                const View y{T.tw.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
+                const View y{T.tw.level[g.out_level].as<h16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout, T.tw.level_lo[g.out_level]};
                 tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_, &fin);
             }
         }
     }
     stats_valid_ = true;
 
-    // ---- loss + gradient at the logits (fp32 planes), then bf16 [positions][8] for the tensor-core backward
+    // ---- loss + gradient at the logits (fp32 planes), then h16 [positions][8] for the tensor-core backward
     k::loss_forward_backward(t_logits_.as<float>(), labels_dev, t_glogits_.as<float>(), n, K, h, w, t_loss_.as<double>(), stream_);
-    tc::planes_to_nhwc8(t_glogits_.as<float>(), K, T.glogits16.as<bf16>(), T.tw.geo[0], stream_);
+    tc::planes_to_nhwc8(t_glogits_.as<float>(), K, T.glogits16.as<h16>(), T.tw.geo[0], stream_, T.loss_scale);
 
     // ---- backward
     for (int l = 0; l <= plan_.levels; ++l)
         if (T.grad_level_needs_zero[l])
-            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(bf16), stream_);
+            k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(h16), stream_);
     const size_t np = plan_.num_params;
     k::fill_zero(G, np * sizeof(float), stream_);
     const int nbuckets = 4;
@@ -453,31 +473,29 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
                 const int mish_first = g.bn_first ? 0 : 1;
                 const float* stats = t_stats_.as<float>() + stats_off_[gi];
                 const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
-                const View dzv{T.dz.as<bf16>() + t.z_off, g.cout, 0, g.cout};
-                const View gy{T.tg.level[g.out_level].as<bf16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
+                const View dzv{T.dz.as<h16>() + t.z_off, g.cout, 0, g.cout};
+                const View gy{T.tg.level[g.out_level].as<h16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
                 tc::bn_backward_reduce_nhwc(z, gy, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
                                             stream_, down);
                 tc::bn_backward_apply_nhwc(z, gy, dzv, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
-                                           G + g.bn_off, G + g.bn_off + g.cout, G + g.b_off, stream_);
+                                           G + g.bn_off, G + g.bn_off + g.cout, G + g.b_off, stream_, 0, unscale);
             } else {
                 // bias gradient = channel sums of the gradient at the conv output (layers.h:226, cpu_dlib.cpp:470-504)
                 const tc::WgradJob& wj = t.wgrad;
-                const View dzv{const_cast<bf16*>(wj.dy), wj.dy_ctot, wj.dy_c0, wj.cy};
+                const View dzv{const_cast<h16*>(wj.dy), wj.dy_ctot, wj.dy_c0, wj.cy};
                 k::fill_zero(T.bias_tmp.p, sizeof(float) * 64, stream_);
-                tc::channel_sum_nhwc(dzv, geo, T.bias_tmp.as<float>(), stream_);
+                tc::channel_sum_nhwc(dzv, geo, T.bias_tmp.as<float>(), stream_, unscale);
                 AB_CUDA(cudaMemcpyAsync(G + g.b_off, T.bias_tmp.p, sizeof(float) * g.cout, cudaMemcpyDeviceToDevice, stream_));
             }
             if (up) {
-                const View xin{T.tw.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
-                tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<bf16>() + t.upx_off, geo, stream_);
+                const View xin{T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<h16>() + t.upx_off, geo, stream_);
             }
-            static const bool wgrad_legacy = getenv("AB_WGRAD_MMA") != nullptr;   // warp-level mma.sync version, kept for A/B runs
-            if (wgrad_legacy) tc::wgrad_mma(t.wgrad, T.wscratch.as<float>(), stream_);
-            else tc::launch_wgrad_tc(t.wgrad_tc, stream_);
+            tc::launch_wgrad_tc(t.wgrad_tc, stream_);
             for (const ConvLaunch& L : t.dgrad) tc::launch_conv(L, stream_);
             if (g.pool_input) {
-                const View gin{T.tg.level[g.in_level].as<bf16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
-                tc::maxpool_backward_nhwc(T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi], g.cin, T.tw.geo[g.in_level], T.dpool.as<bf16>() + t.dpool_off,
+                const View gin{T.tg.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                tc::maxpool_backward_nhwc(T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi], g.cin, T.tw.geo[g.in_level], T.dpool.as<h16>() + t.dpool_off,
                                           geo, gin, stream_);
             }
         }

@@ -219,7 +219,7 @@ void Engine::train_step_device(const uint8_t* imgs_dev, const void* labels_dev, 
     if (!model_.is_training) throw state_error("StartTraining needs a training net (net_type with bn_ layers)");
     AB_CUDA(cudaSetDevice(device_));
     level_dims(h, w, plan_.levels);   // rejects non-canonical sizes
-    if (precision_ == 1) { tc_train_step(imgs_dev, labels_dev, n, h, w, update); return; }   // AB_PRECISION_BF16: tensor-core path
+    if (precision_ == 1) { tc_train_step(imgs_dev, labels_dev, n, h, w, update); return; }   // AB_PRECISION_F16: tensor-core path
     ensure_train_ws(n, h, w);
     to_tensor(imgs_dev, t_x_.as<float>(), n, h, w, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
     forward_train(n, h, w);

@@ -1,0 +1,23 @@
+// fp16 conversion helpers of the tensor-core path (tc.h): saturating float -> half2 packs (an overflow becomes +-65504,
+// never inf: a later 0 * inf would poison a whole step) and the hi + lo split of the training forward pass.
+#pragma once
+#include <cuda_fp16.h>
+
+namespace ab {
+namespace tc {
+
+__device__ __forceinline__ __half2 sat_half2(float a, float b)
+{
+    const __half2 lim = __floats2half2_rn(65504.f, 65504.f);
+    return __hmax2(__hmin2(__floats2half2_rn(a, b), lim), __hneg2(lim));
+}
+// a = hi + lo up to 2^-22 |a| (|a| inside fp16's normal range; below it lo keeps the absolute error under 2^-25)
+__device__ __forceinline__ void split_half2(float a, float b, __half2& hi, __half2& lo)
+{
+    hi = sat_half2(a, b);
+    const float2 h = __half22float2(hi);
+    lo = __floats2half2_rn(a - h.x, b - h.y);
+}
+
+}  // namespace tc
+}  // namespace ab

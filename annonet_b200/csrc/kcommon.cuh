@@ -11,7 +11,20 @@ namespace k {
 extern std::atomic<unsigned long long> g_launches;  // kernels of this library launched so far
 inline void count_launch(int n = 1) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
-constexpr int kNumSMs = 148;
+// SM count of the current device (B200: 148), queried once: sizes the persistent grids, the tiling cost model and the
+// split-K scratch, so a MIG slice or another Blackwell SKU gets grids that fit it
+inline int num_sms()
+{
+    static const int n = [] {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) {
+            cudaGetLastError();
+            return 148;
+        }
+        return v;
+    }();
+    return n;
+}
 
 // mish_: y = x - 2x/(e^2 + 2e + 2), e = exp(x)   (cpu_dlib.cpp:1510-1523; fp32 exp overflow -> y = x)
 __device__ __forceinline__ float mish_f(float x)

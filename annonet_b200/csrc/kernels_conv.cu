@@ -1,4 +1,4 @@
-// fp32 implicit-GEMM convolutions on the FMA pipe (the exact-parity path; the bf16 tcgen05 path is
+// fp32 implicit-GEMM convolutions on the FMA pipe (the exact-parity path; the h16 tcgen05 path is
 // kernels_tc.cu).  Direct form: a CTA owns a TW x TH pixel tile of one sample and CO_T output
 // channels; input channels stream through shared memory 8 at a time (patch with a 1-pixel halo +
 // the 8x9xCO_T filter slab); each thread keeps a 4-pixel x CO_T register tile.

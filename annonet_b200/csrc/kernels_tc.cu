@@ -1,4 +1,4 @@
-// bf16 tcgen05 / TMEM / TMA implicit-GEMM convolution (AB_PRECISION_BF16): con_ / cont_ forward and
+// fp16 tcgen05 / TMEM / TMA implicit-GEMM convolution (AB_PRECISION_F16): con_ / cont_ forward and
 // backward-data (dnn/layers.h:196-229,521-554; cpu_dlib.cpp:2250-2325) as ONE shifted-window GEMM kernel
 // over the padded flat NHWC layout described in tc.h:
 //
@@ -10,6 +10,7 @@
 //   warp 0  : TMA producer (one elected lane)          full/empty mbarrier ring
 //   warp 1  : TMEM allocation + tcgen05.mma issue (one elected lane), tcgen05.commit releases stages
 //   warps 2-5: epilogue, tcgen05.ld of the fp32 accumulators -> bias / mish / affine -> global
+#include "h16.cuh"
 #include "kcommon.cuh"
 #include "tc.h"
 
@@ -109,8 +110,8 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32
         "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 
-// mish for the bf16 path: x - 2x / (e^2 + 2e + 2), e = exp(x), on the raw MUFU approximations (results are rounded
-// to bf16 anyway).  e = inf -> rcp = 0 -> x;  e = 0 -> x - x = 0.
+// mish for the h16 path: x - 2x / (e^2 + 2e + 2), e = exp(x), on the raw MUFU approximations (results are rounded
+// to h16 anyway).  e = inf -> rcp = 0 -> x;  e = 0 -> x - x = 0.
 __device__ __forceinline__ float mish_fast(float x)
 {
     float e, rc;
@@ -174,21 +175,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                     mbar_wait(&empty_bar[s], ((it / L.stages) & 1) ^ 1);
                     mbar_expect(&full_bar[s], tx);
                     const uint32_t a_s = smem0 + (uint32_t)s * L.stage_bytes, b_s = a_s + L.a_stage_bytes;
-                    const int c = L.a_c0 + ch * L.kc;
+                    // split operands: part 0 = A_hi W_hi, 1 = A_lo W_hi, 2 = A_hi W_lo (tc.h)
+                    const int part = ch / L.nch1, c1 = ch - part * L.nch1;
+                    const int c = L.a_c0 + c1 * L.kc;
+                    const int arow = o0 + (part == 1 ? (int)L.a_lo_rows : 0);
                     for (int sg = 0; sg < L.nseg; ++sg)
                         for (int l = 0; l < L.nloads; ++l)
                             tma_2d(a_s + (uint32_t)(sg * L.seg_alloc + l * L.box_rows) * pitch, &L.tmA, c,
-                                   o0 + L.seg_pos[sg] + l * L.box_rows, &full_bar[s]);
+                                   arow + L.seg_pos[sg] + l * L.box_rows, &full_bar[s]);
+                    const int bk = part * L.kpart + c1 * L.kc;
 #pragma unroll
                     for (int t = 0; t < NTAPS; ++t)
-                        tma_2d(b_s + (uint32_t)(t * L.nblk) * pitch, &L.tmB, ch * L.kc, t * L.npad_total + n0, &full_bar[s]);
+                        tma_2d(b_s + (uint32_t)(t * L.nblk) * pitch, &L.tmB, bk, t * L.npad_total + n0, &full_bar[s]);
                 }
             }
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            // instruction descriptor: D f32, A/B bf16, both K-major, N = nblk, M = 128
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(L.nblk >> 3) << 17) | ((128u >> 4) << 24);
+            // instruction descriptor: D f32 (bit 4), A/B fp16 (format 0 in bits 7-9 / 10-12), both K-major, N = nblk, M = 128
+            const uint32_t idesc = (1u << 4) | ((uint32_t)(L.nblk >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t desc_hi = (uint32_t)(smem_desc_hi(pitch) >> 32);
             const uint32_t lbo = 1u << 16;
             const int ksteps = L.kc / 16, th = L.th, nblk = L.nblk, nchunks = L.nchunks, stages = L.stages;
@@ -380,11 +385,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         if (okB && c0ok) *reinterpret_cast<float4*>(ob) = odd ? make_float4(v[4], v[5], v[6], v[7]) : make_float4(rcv[0], rcv[1], rcv[2], rcv[3]);
                         if (okB && c1ok) *reinterpret_cast<float4*>(ob + 8) = odd ? make_float4(v[12], v[13], v[14], v[15]) : make_float4(rcv[4], rcv[5], rcv[6], rcv[7]);
                     } else {
-                        // bf16 row block = two 16-byte halves (8 channels each); even lane writes half 0 of both rows, odd lane half 1
+                        // h16 row block = two 16-byte halves (8 channels each); even lane writes half 0 of both rows, odd lane half 1
                         const int ho = odd ? 8 : 0;
                         const bool cok = co0 + ho < L.cout;
-                        bf16* oa = (bf16*)L.out + posA * L.out_ctot + L.out_c0 + co0 + ho;
-                        bf16* ob = (bf16*)L.out + posB * L.out_ctot + L.out_c0 + co0 + ho;
+                        h16* oa = (h16*)L.out + posA * L.out_ctot + L.out_c0 + co0 + ho;
+                        h16* ob = (h16*)L.out + posB * L.out_ctot + L.out_c0 + co0 + ho;
                         if (accum) {
                             uint4 oldA = make_uint4(0, 0, 0, 0), oldB = make_uint4(0, 0, 0, 0);
                             if (okA && cok) oldA = *reinterpret_cast<const uint4*>(oa);
@@ -392,32 +397,36 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                             float rcv[8];
 #pragma unroll
                             for (int i = 0; i < 8; ++i) rcv[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i] : v[8 + i], 1);
-                            const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&oldA);
-                            const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&oldB);
-                            __nv_bfloat162 ra[4], rb[4];
+                            const __half2* pa = reinterpret_cast<const __half2*>(&oldA);
+                            const __half2* pb = reinterpret_cast<const __half2*>(&oldB);
+                            __half2 ra[4], rb[4];
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                const float2 fa = __bfloat1622float2(pa[i]), fb = __bfloat1622float2(pb[i]);
+                                const float2 fa = __half22float2(pa[i]), fb = __half22float2(pb[i]);
                                 // row A's values: odd lane got them from its partner; row B's: even lane did
                                 const float a0 = odd ? rcv[2 * i] : v[2 * i], a1 = odd ? rcv[2 * i + 1] : v[2 * i + 1];
                                 const float b0 = odd ? v[8 + 2 * i] : rcv[2 * i], b1 = odd ? v[8 + 2 * i + 1] : rcv[2 * i + 1];
-                                ra[i] = __floats2bfloat162_rn(fa.x + a0, fa.y + a1);
-                                rb[i] = __floats2bfloat162_rn(fb.x + b0, fb.y + b1);
+                                ra[i] = sat_half2(fa.x + a0, fa.y + a1);
+                                rb[i] = sat_half2(fb.x + b0, fb.y + b1);
                             }
                             if (okA && cok) *reinterpret_cast<uint4*>(oa) = *reinterpret_cast<const uint4*>(ra);
                             if (okB && cok) *reinterpret_cast<uint4*>(ob) = *reinterpret_cast<const uint4*>(rb);
                         } else {
-                            __nv_bfloat162 pk[8];
+                            __half2 pk[8], pl[8];
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) pk[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-                            const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
-                            uint32_t rc[4];
+                            for (int i = 0; i < 8; ++i) split_half2(v[2 * i], v[2 * i + 1], pk[i], pl[i]);
+                            // hi halves, then (split tensors) the rounding residuals lo_off elements behind
+                            for (int half_i = 0; half_i < (L.out_lo_off ? 2 : 1); ++half_i) {
+                                const uint32_t* pw = reinterpret_cast<const uint32_t*>(half_i ? pl : pk);
+                                uint32_t rc[4];
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) rc[i] = __shfl_xor_sync(0xffffffffu, odd ? pw[i] : pw[4 + i], 1);
-                            const uint4 mine0 = make_uint4(pw[0], pw[1], pw[2], pw[3]), mine1 = make_uint4(pw[4], pw[5], pw[6], pw[7]);
-                            const uint4 got = make_uint4(rc[0], rc[1], rc[2], rc[3]);
-                            if (okA && cok) *reinterpret_cast<uint4*>(oa) = odd ? got : mine0;
-                            if (okB && cok) *reinterpret_cast<uint4*>(ob) = odd ? mine1 : got;
+                                for (int i = 0; i < 4; ++i) rc[i] = __shfl_xor_sync(0xffffffffu, odd ? pw[i] : pw[4 + i], 1);
+                                const uint4 mine0 = make_uint4(pw[0], pw[1], pw[2], pw[3]), mine1 = make_uint4(pw[4], pw[5], pw[6], pw[7]);
+                                const uint4 got = make_uint4(rc[0], rc[1], rc[2], rc[3]);
+                                const long long lo = half_i ? L.out_lo_off : 0;
+                                if (okA && cok) *reinterpret_cast<uint4*>(oa + lo) = odd ? got : mine0;
+                                if (okB && cok) *reinterpret_cast<uint4*>(ob + lo) = odd ? mine1 : got;
+                            }
                         }
                     }
                 }
@@ -450,7 +459,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(L.tmem_cols));
 }
 
-__global__ void pack_filters_kernel(const float* __restrict__ w, bf16* __restrict__ packed, int nreal, int npad, int kreal, int kp,
+__global__ void pack_filters_kernel(const float* __restrict__ w, h16* __restrict__ packed, int nreal, int npad, int kreal, int kp,
                                     int ntaps, long long sn, long long sk, int t0, int t1, int t2, int t3, int t4, int t5, int t6,
                                     int t7, int t8)
 {
@@ -462,7 +471,7 @@ __global__ void pack_filters_kernel(const float* __restrict__ w, bf16* __restric
         const int t = (int)(i / ((long long)kp * npad));
         float v = 0.f;
         if (n < nreal && kidx < kreal) v = w[n * sn + kidx * sk + tapmap[t]];
-        packed[i] = __float2bfloat16(v);
+        packed[i] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
     }
 }
 
@@ -488,7 +497,7 @@ void make_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int
     cuuint64_t strides[1] = {(cuuint64_t)ctot * 2};
     cuuint32_t box[2] = {(cuuint32_t)kc, (cuuint32_t)box_rows}, es[2] = {1, 1};
     const CUtensorMapSwizzle sw = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
-    const CUresult r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
+    const CUresult r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
                                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         throw std::runtime_error("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + "): rows " + std::to_string(rows) + " ctot " +
@@ -507,7 +516,7 @@ int padded_k(int cin) { return (cin + 63) / 64 * 64; }
 
 size_t packed_filter_elems(int cin, int npad_total, int ntaps) { return (size_t)ntaps * npad_total * padded_k(cin); }
 
-void pack_filters_bf16(const float* w, bf16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
+void pack_filters_bf16(const float* w, h16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
                        long long sk, cudaStream_t st)
 {
     const int kp = padded_k(kreal);
@@ -523,7 +532,8 @@ void pack_filters_bf16(const float* w, bf16* packed, int nreal, int npad_total, 
 void setup_conv(ConvLaunch& L, const ConvSetup& s)
 {
     if (s.cin % 8 || s.src_ctot % 8 || s.a_c0 % 8)
-        throw std::invalid_argument("the bf16 tensor-core path needs channel counts that are multiples of 8");
+        throw std::invalid_argument("the tensor-core path needs channel counts that are multiples of 8");
+    const int parts = s.split ? 3 : 1;
     L.a_c0 = s.a_c0;
     L.ntaps = s.ntaps;
     L.npad_total = s.npad_total;
@@ -532,7 +542,8 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     L.nblk = ((s.npad_total + nblocks - 1) / nblocks + 15) / 16 * 16;
     nblocks = (s.npad_total + L.nblk - 1) / L.nblk;
     if (nblocks * L.nblk != s.npad_total) throw std::logic_error("N blocks must tile the padded N");
-    if (s.grid.positions() + 4096 >= (1ll << 31)) throw std::invalid_argument("tensor too large for the bf16 conv kernel (positions must fit 31 bits)");
+    if (s.grid.positions() * (s.split ? 2 : 1) + 4096 >= (1ll << 31))
+        throw std::invalid_argument("tensor too large for the tcgen05 conv kernel (positions must fit 31 bits)");
     const int P = s.grid.P();
     L.total = (long long)s.grid.N * s.grid.S();
     L.S = s.grid.S(); L.P = P; L.H = s.grid.H; L.W = s.grid.W; L.Nsamples = s.grid.N;
@@ -557,7 +568,7 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     static const int force_mode = getenv("AB_TC_MODE") ? atoi(getenv("AB_TC_MODE")) : -1;
     for (int kc : {16, 32, 64}) {
         if (force_kc && kc != force_kc && s.cin >= force_kc) continue;
-        const int kpad = (s.cin + kc - 1) / kc * kc, nchunks = kpad / kc, pitch = kc * 2;
+        const int kpad = (s.cin + kc - 1) / kc * kc, nchunks = kpad / kc * parts, pitch = kc * 2;
         for (int rows_mode = 0; rows_mode < 3; ++rows_mode) {   // 0 FLAT, 1 ROWS, 2 ROWS + merged dy taps
             if (rows_mode && P < 128) continue;
             if (rows_mode == 2 && (!kym_ok || no_kym)) continue;
@@ -602,7 +613,7 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
                 // data-gradient conv at kc 64 / 1 stage took 5.7k cycles per item against 2.4k modelled without this term).
                 const double t_front = std::max(std::max(t_tma, t_mma), (t_tma + t_mma + 1800.0 * nchunks) / stages);
                 const double t_item = two ? std::max(t_front, t_epi) : std::max(t_front, t_mma + t_epi);
-                const long long rounds = (ctas * nblocks + k::kNumSMs - 1) / k::kNumSMs;
+                const long long rounds = (ctas * nblocks + k::num_sms() - 1) / k::num_sms();
                 (void)waste; (void)loadf;
                 double cost = (double)rounds * t_item + 3000.0;   // + pipeline fill / drain
                 cost *= 1.0 + 0.01 * (kc == 16 ? 2 : kc == 32 ? 1 : 0);  // ties: fewer, larger TMA boxes
@@ -612,7 +623,10 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     }
     if (best.kc == 0) throw std::logic_error("no tcgen05 conv tiling fits shared memory");
     L.kc = best.kc;
-    L.nchunks = (s.cin + L.kc - 1) / L.kc;
+    L.nch1 = (s.cin + L.kc - 1) / L.kc;
+    L.nchunks = L.nch1 * parts;
+    L.kpart = padded_k(s.cin);
+    L.a_lo_rows = s.split ? s.src_positions : 0;
     L.rows_mode = best.rows_mode != 0; L.kym = best.rows_mode == 2; L.th = best.th; L.nseg = best.nseg; L.nloads = best.nloads; L.box_rows = best.box_rows;
     L.seg_alloc = best.nloads * best.box_rows;
     L.a_stage_bytes = best.a_bytes; L.stage_bytes = best.stage_bytes; L.stages = std::max(best.stages, 1);
@@ -638,8 +652,9 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
         fprintf(stderr, "tc conv: P %d cin %d npad %d taps %d -> kc %d %s th %d nseg %d seg %d stages %d smem %u ctas %lld cost %.1f\n", P, s.cin,
                 s.npad_total, s.ntaps, L.kc, L.kym ? "KYM" : L.rows_mode ? "ROWS" : "FLAT", L.th, L.nseg, L.seg_alloc, L.stages, L.smem_bytes, best.ctas, best.cost);
     // activations: 64-byte L2 promotion -- a narrow channel slice costs 64 B of HBM traffic per position instead of 128 (experiments/tma_bench.cu)
-    make_map_2d(&L.tmA, s.src, s.src_positions, s.src_ctot, L.kc, L.box_rows, L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
-    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * s.npad_total, padded_k(s.cin), L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    make_map_2d(&L.tmA, s.src, s.src_positions * (s.split ? 2 : 1), s.src_ctot, L.kc, L.box_rows,
+                L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * s.npad_total, padded_k(s.cin) * parts, L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
 }
 
 template <int NTAPS>
@@ -651,7 +666,7 @@ static void launch_conv_t(const ConvLaunch& L, cudaStream_t st, int rev)
         attr_set = true;
     }
     const long long items = L.grid_x * (L.npad_total / L.nblk);
-    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::kNumSMs), kThreads, L.smem_bytes, st>>>(L, rev);
+    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::num_sms()), kThreads, L.smem_bytes, st>>>(L, rev);
 }
 
 void launch_conv(const ConvLaunch& L, cudaStream_t st, int rev)

@@ -1,4 +1,4 @@
-// Training-side bf16 NHWC ("padded flat", tc.h) elementwise / reduction kernels of the tensor-core path:
+// Training-side fp16 NHWC ("padded flat", tc.h) elementwise / reduction kernels of the tensor-core path:
 // batch normalisation in CONV_MODE fused with mish (cpu_dlib.cpp:1073-1289,1510-1558), the max-pool gradient
 // (cpu_dlib.cpp:1971-2017), bias gradients (cpu_dlib.cpp:470-504) and the small layout conversions around them.
 // All HBM-bound: 16-byte accesses of 8 channels, fp32 arithmetic, per-channel reductions in registers ->
@@ -6,6 +6,7 @@
 //
 // Thread mapping of the per-channel kernels: blockDim = (C/8, TY); threadIdx.x owns 8 consecutive channels for the
 // whole kernel, threadIdx.y strides over positions, so a warp reads consecutive 16-byte vectors of [pos][C].
+#include "h16.cuh"
 #include "kcommon.cuh"
 #include "tc.h"
 
@@ -16,23 +17,28 @@ namespace ab {
 namespace tc {
 namespace {
 
-struct alignas(16) BF8 { __nv_bfloat162 v[4]; };
+struct alignas(16) BF8 { __half2 v[4]; };
 
 __device__ __forceinline__ void unpack8(const BF8& b, float f[8])
 {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(b.v[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+    for (int i = 0; i < 4; ++i) { const float2 t = __half22float2(b.v[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
 }
 __device__ __forceinline__ BF8 pack8(const float f[8])
 {
     BF8 b;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) b.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    for (int i = 0; i < 4; ++i) b.v[i] = sat_half2(f[2 * i], f[2 * i + 1]);
     return b;
 }
-// 8 bf16 of a channel slice.  The slice is 16..64 bytes of a wider row: ask L2 for 64-byte fetches instead of whole 128-byte
+__device__ __forceinline__ void split8(const float f[8], BF8& hi, BF8& lo)
+{
+#pragma unroll
+    for (int i = 0; i < 4; ++i) split_half2(f[2 * i], f[2 * i + 1], hi.v[i], lo.v[i]);
+}
+// 8 h16 of a channel slice.  The slice is 16..64 bytes of a wider row: ask L2 for 64-byte fetches instead of whole 128-byte
 // lines (ncu: the backward bn passes read 269 MB of DRAM for a 67 MB slice, 4 x the algorithmic bytes)
-__device__ __forceinline__ BF8 ld8(const bf16* p)
+__device__ __forceinline__ BF8 ld8(const h16* p)
 {
     BF8 r;
     uint32_t* u = reinterpret_cast<uint32_t*>(&r);
@@ -44,12 +50,12 @@ __device__ __forceinline__ void ldf8(const float* p, float f[8])
     const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
     f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
 }
-__device__ __forceinline__ void st8(bf16* p, const BF8& v) { *reinterpret_cast<BF8*>(p) = v; }
+__device__ __forceinline__ void st8(h16* p, const BF8& v) { *reinterpret_cast<BF8*>(p) = v; }
 
 struct GeoD { int N, H, W, P; unsigned S; long long total; };  // total = N * S  (< 2^31: checked by geod)
 GeoD geod(const Geo& g)
 {
-    if (g.positions() >= (1ll << 31)) throw std::invalid_argument("tensor too large for the bf16 NHWC kernels (positions must fit 31 bits)");
+    if (g.positions() >= (1ll << 31)) throw std::invalid_argument("tensor too large for the h16 NHWC kernels (positions must fit 31 bits)");
     return GeoD{g.N, g.H, g.W, g.P(), (unsigned)g.S(), (long long)g.N * g.S()};
 }
 
@@ -61,7 +67,7 @@ __device__ __forceinline__ bool is_pixel(const GeoD& g, long long pos)
     return rem >= (unsigned)g.P && (rem % (unsigned)g.P) != 0;
 }
 
-// mish_ (cpu_dlib.cpp:1510-1558) on the fast-math intrinsics: the results feed bf16 tensors or fp32 sums of bf16-rounded
+// mish_ (cpu_dlib.cpp:1510-1558) on the fast-math intrinsics: the results feed h16 tensors or fp32 sums of h16-rounded
 // data, so 2-ulp exp / division are far below the path's rounding noise.  e = inf -> r = 0 -> y = x.
 __device__ __forceinline__ float mish_fast(float x)
 {
@@ -151,8 +157,8 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
 }
 
 // y = mish_first ? mish(z)*sc + sh : mish(z*sc + sh),   sc = gamma*invstd, sh = beta - mean*sc
-__global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, bf16* __restrict__ y, int y_ctot,
-                                                            int y_c0, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
+__global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, h16* __restrict__ y, int y_ctot,
+                                                            int y_c0, long long y_lo, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, const float* __restrict__ stats,
                                                             const BnFinalize fin, int rev)
 {
@@ -218,13 +224,17 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
                 if (has_mish && !mish_first) v = mish_fast(v);
                 f[u][i] = v;
             }
-            st8(y + (rev ? g.total - 1 - (p0 + u * stride) : p0 + u * stride) * y_ctot + y_c0 + c, pack8(f[u]));
+            h16* yp = y + (rev ? g.total - 1 - (p0 + u * stride) : p0 + u * stride) * y_ctot + y_c0 + c;
+            BF8 hi, lo;
+            split8(f[u], hi, lo);
+            st8(yp, hi);
+            if (y_lo) st8(yp + y_lo, lo);   // split tensor (training forward): the rounding residual
         }
     }
 }
 
 // xhat = x*I + M (I = invstd, M = -mean*invstd);  conv->bn->mish layers: dv *= mish'(xhat*gamma + beta)
-__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
+__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const h16* __restrict__ gy,
                                                                  int gy_ctot, int gy_c0, long long npos, int mish_first, int has_mish,
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                  const float* __restrict__ stats, double* __restrict__ red, int rev)
@@ -252,7 +262,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __
 #pragma unroll
                 for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) dq[u].v[i] = __floats2bfloat162_rn(0.f, 0.f);   // dv = 0: adds nothing
+                for (int i = 0; i < 4; ++i) dq[u].v[i] = __floats2half2_rn(0.f, 0.f);   // dv = 0: adds nothing
             }
         }
         float ci[8], cm[8];
@@ -286,12 +296,12 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __
 //   dvars = -0.5*gamma*invstd^2 * sum(dv*xhat),  dmeans = -gamma*invstd * sum(dv)
 //   r = dv*k1 + k2*x + k3,   k1 = gamma*invstd,  k2 = 2*dvars/num,  k3 = dmeans/num - k2*mean
 // conv->mish->bn layers: x = mish(z), dz = r*mish'(z);   conv->bn->mish layers: x = z, dv *= mish'(x*A + B) first
-__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const bf16* __restrict__ gy,
-                                                                int gy_ctot, int gy_c0, bf16* __restrict__ dz, int dz_ctot, int dz_c0, GeoD g,
+__global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, const h16* __restrict__ gy,
+                                                                int gy_ctot, int gy_c0, h16* __restrict__ dz, int dz_ctot, int dz_c0, GeoD g,
                                                                 int mish_first, int has_mish, const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, const float* __restrict__ stats,
                                                                 const double* __restrict__ red, float invnum, float* __restrict__ dgamma,
-                                                                float* __restrict__ dbeta, float* __restrict__ dbias, int rev)
+                                                                float* __restrict__ dbeta, float* __restrict__ dbias, int rev, float unscale)
 {
     __shared__ __align__(16) float s_k1[kMaxC], s_k2[kMaxC], s_k3[kMaxC], s_a[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
@@ -305,7 +315,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
         s_k3[i] = dmeans * invnum - k2 * mean;
         s_a[i] = invstd * ga;
         s_b[i] = be - mean * invstd * ga;
-        if (blockIdx.x == 0) { dgamma[i] = s_dvx; dbeta[i] = s_dv; }
+        if (blockIdx.x == 0) { dgamma[i] = s_dvx * unscale; dbeta[i] = s_dv * unscale; }
     }
     __syncthreads();
     const bool act_after = has_mish && !mish_first, act_before = has_mish && mish_first;
@@ -348,11 +358,14 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
             st8(dz + (rev ? g.total - 1 - (p0 + u * stride) : p0 + u * stride) * dz_ctot + dz_c0 + c, pack8(d));
         }
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[0][i] *= unscale;
     float* const dst[1] = {dbias};
     block_reduce_channels<1, float>(acc, dst);
 }
 
-__global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const bf16* __restrict__ v, int ctot, int c0, long long npos, float* __restrict__ out)
+__global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const h16* __restrict__ v, int ctot, int c0, long long npos, float* __restrict__ out,
+                                                            float unscale)
 {
     float acc[1][8] = {};
     for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < npos; pos += (long long)gridDim.x * blockDim.y) {
@@ -361,6 +374,8 @@ __global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const bf16* __restri
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[0][i] += f[i];
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[0][i] *= unscale;
     float* const dst[1] = {out};
     block_reduce_channels<1, float>(acc, dst);
 }
@@ -368,7 +383,7 @@ __global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const bf16* __restri
 // gather form: an input pixel belongs to at most 2 x 2 windows and receives a window's gradient iff it is that window's
 // first maximum in row-major order -- which element won is read from the byte map the forward pass wrote
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restrict__ arg, int C8, int N, int Hi, int Wi,
-                                                          const bf16* __restrict__ gout, int Ho, int Wo, bf16* __restrict__ gin, int gin_ctot,
+                                                          const h16* __restrict__ gout, int Ho, int Wo, h16* __restrict__ gin, int gin_ctot,
                                                           int gin_c0)
 {
     const long long total = (long long)N * Hi * Wi * C8;
@@ -401,7 +416,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restr
             }
         }
     if (!any) return;
-    bf16* gp = gin + (n * Si + (long long)(y + 1) * (Wi + 1) + (x + 1)) * gin_ctot + gin_c0 + cg * 8;
+    h16* gp = gin + (n * Si + (long long)(y + 1) * (Wi + 1) + (x + 1)) * gin_ctot + gin_c0 + cg * 8;
     float old[8];
     unpack8(ld8(gp), old);
 #pragma unroll
@@ -409,7 +424,8 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restr
     st8(gp, pack8(old));
 }
 
-__global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __restrict__ planes, int K, bf16* __restrict__ out, int N, int H, int W)
+__global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __restrict__ planes, int K, h16* __restrict__ out, int N, int H, int W,
+                                                              float scale)
 {
     const long long hw = (long long)H * W;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -418,13 +434,13 @@ __global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __res
     const long long rem = i - n * hw;
     const int y = (int)(rem / W), x = (int)(rem - (long long)y * W);
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int k = 0; k < K && k < 8; ++k) f[k] = planes[((long long)n * K + k) * hw + rem];
+    for (int k = 0; k < K && k < 8; ++k) f[k] = planes[((long long)n * K + k) * hw + rem] * scale;
     const long long pos = n * (long long)(H + 1) * (W + 1) + (long long)(y + 1) * (W + 1) + (x + 1);
     st8(out + pos * 8, pack8(f));
 }
 
-__global__ void __launch_bounds__(256) upsample_zero_kernel(const bf16* __restrict__ in, int in_ctot, int in_c0, int C8, int N, int h, int w,
-                                                            bf16* __restrict__ out)
+__global__ void __launch_bounds__(256) upsample_zero_kernel(const h16* __restrict__ in, int in_ctot, int in_c0, int C8, int N, int h, int w,
+                                                            h16* __restrict__ out)
 {
     const int Hf = 2 * h + 1, Wf = 2 * w + 1;
     const long long total = (long long)N * Hf * Wf * C8;
@@ -437,25 +453,28 @@ __global__ void __launch_bounds__(256) upsample_zero_kernel(const bf16* __restri
     const int n = (int)(p / Hf);
     BF8 v;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) v.v[k] = __floats2bfloat162_rn(0.f, 0.f);
+    for (int k = 0; k < 4; ++k) v.v[k] = __floats2half2_rn(0.f, 0.f);
     if (!(y & 1) && !(x & 1) && (y >> 1) < h && (x >> 1) < w)
         v = ld8(in + (n * (long long)(h + 1) * (w + 1) + (long long)((y >> 1) + 1) * (w + 1) + ((x >> 1) + 1)) * in_ctot + in_c0 + cg * 8);
     st8(out + (n * (long long)(Hf + 1) * (Wf + 1) + (long long)(y + 1) * (Wf + 1) + (x + 1)) * (C8 * 8) + cg * 8, v);
 }
 
-__global__ void __launch_bounds__(256) pack_batched_kernel(const float* __restrict__ arena, bf16* __restrict__ packs, const PackJob* __restrict__ jobs)
+__global__ void __launch_bounds__(256) pack_batched_kernel(const float* __restrict__ arena, h16* __restrict__ packs, const PackJob* __restrict__ jobs)
 {
     const PackJob& j = jobs[blockIdx.y];
-    const long long total = (long long)j.ntaps * j.npad * j.kp;
+    const int kpt = j.kp * j.parts;   // K extent of a packed row: [hi | hi | lo] when the operands are split
+    const long long total = (long long)j.ntaps * j.npad * kpt;
     const float* w = arena + j.w_off;
-    bf16* packed = packs + j.packed_off;
+    h16* packed = packs + j.packed_off;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int kidx = (int)(i % j.kp);
-        const int n = (int)((i / j.kp) % j.npad);
-        const int t = (int)(i / ((long long)j.kp * j.npad));
+        const int kk = (int)(i % kpt);
+        const int part = kk / j.kp, kidx = kk - part * j.kp;
+        const int n = (int)((i / kpt) % j.npad);
+        const int t = (int)(i / ((long long)kpt * j.npad));
         float v = 0.f;
         if (n < j.nreal && kidx < j.kreal) v = w[n * j.sn + kidx * j.sk + j.tapmap[t]];
-        packed[i] = __float2bfloat16(v);
+        const h16 hi = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+        packed[i] = part == 2 ? __float2half_rn(v - __half2float(hi)) : hi;
     }
 }
 
@@ -465,10 +484,10 @@ struct Shape { dim3 block; unsigned grid; };
 Shape channel_shape(int C, long long npos, int ctas_per_sm = 8)
 {
     const int C8 = C / 8;
-    if (C % 8 || C8 < 1 || C8 > 32) throw std::invalid_argument("bf16 NHWC kernels need 8 <= C <= 256, C % 8 == 0");
+    if (C % 8 || C8 < 1 || C8 > 32) throw std::invalid_argument("h16 NHWC kernels need 8 <= C <= 256, C % 8 == 0");
     const int TY = kMaxT / C8;
     const long long want = (npos + TY - 1) / TY;
-    return Shape{dim3(C8, TY), (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)k::kNumSMs * ctas_per_sm))};
+    return Shape{dim3(C8, TY), (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)k::num_sms() * ctas_per_sm))};
 }
 
 }  // namespace
@@ -487,9 +506,9 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
                    const float* stats, cudaStream_t st, const BnFinalize* fin, int rev)
 {
     const GeoD d = geod(g);
-    k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
+    k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, (y.lo_off ? 8.0 : 6.0) * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 4);
-    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
+    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
     k::count_launch();
 }
 
@@ -507,27 +526,27 @@ void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int m
 
 void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, const Geo& g, int mish_first, int has_mish, const float* gamma,
                             const float* beta, const float* stats, const double* red, float* dgamma, float* dbeta, float* dbias,
-                            cudaStream_t st, int rev)
+                            cudaStream_t st, int rev, float unscale)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 8.0 * g.N * g.H * g.W * z.C, 6.0 * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 3);
     const float invnum = 1.0f / (float)((long long)g.N * g.H * g.W);
     bn_bwd_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, dz.p, dz.ctot, dz.c0, d, mish_first, has_mish, gamma, beta, stats, red,
-                                                    invnum, dgamma, dbeta, dbias, rev);
+                                                    invnum, dgamma, dbeta, dbias, rev, unscale);
     k::count_launch();
 }
 
-void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st)
+void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st, float unscale)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 1.0 * g.N * g.H * g.W * v.C, 2.0 * g.N * g.H * g.W * v.C, st);
     const Shape s = channel_shape(v.C, d.total);
-    channel_sum_kernel<<<s.grid, s.block, 0, st>>>(v.p, v.ctot, v.c0, d.total, out);
+    channel_sum_kernel<<<s.grid, s.block, 0, st>>>(v.p, v.ctot, v.c0, d.total, out, unscale);
     k::count_launch();
 }
 
-void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st)
+void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* gout_dense, const Geo& go, const View& gin, cudaStream_t st)
 {
     const long long n = (long long)gi.N * gi.H * gi.W * (C / 8);
     if (n >= (1ll << 31) * 8) throw std::invalid_argument("maxpool_backward_nhwc: tensor too large");
@@ -536,16 +555,16 @@ void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const bf16*
     k::count_launch();
 }
 
-void planes_to_nhwc8(const float* planes, int K, bf16* out, const Geo& g, cudaStream_t st)
+void planes_to_nhwc8(const float* planes, int K, h16* out, const Geo& g, cudaStream_t st, float scale)
 {
     if (K > 8) throw std::invalid_argument("planes_to_nhwc8: at most 8 planes");
     const long long n = (long long)g.N * g.H * g.W;
     k::ProfScope ps(k::F_PACK, 0, (4.0 * K + 16.0) * n, st);
-    planes_to_nhwc8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(planes, K, out, g.N, g.H, g.W);
+    planes_to_nhwc8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(planes, K, out, g.N, g.H, g.W, scale);
     k::count_launch();
 }
 
-void upsample_zero_nhwc(const View& in, const Geo& gc, bf16* out, const Geo& gf, cudaStream_t st)
+void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, cudaStream_t st)
 {
     if (gf.H != 2 * gc.H + 1 || gf.W != 2 * gc.W + 1) throw std::logic_error("upsample_zero_nhwc: geometry mismatch");
     const long long n = (long long)gf.N * gf.H * gf.W * (in.C / 8);
@@ -554,7 +573,7 @@ void upsample_zero_nhwc(const View& in, const Geo& gc, bf16* out, const Geo& gf,
     k::count_launch();
 }
 
-void pack_filters_batched(const float* arena, bf16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st)
+void pack_filters_batched(const float* arena, h16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st)
 {
     if (njobs <= 0) return;
     k::ProfScope ps(k::F_PACK, 0, 0, st);

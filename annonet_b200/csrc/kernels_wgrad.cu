@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(256) channel_sum_kernel(const Slice A, const i
 
 int pick_splits(long long work_items, int cta_per_split)
 {
-    long long s = (2 * kNumSMs + cta_per_split - 1) / cta_per_split;
+    long long s = (2 * num_sms() + cta_per_split - 1) / cta_per_split;
     if (s > work_items) s = work_items;
     if (s < 1) s = 1;
     return (int)s;

@@ -30,7 +30,6 @@ namespace {
 
 constexpr int kWThreads = 192;
 constexpr int kWMaxStages = 4;
-constexpr int kMaxSplitTilesTc = 148;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* b, int n) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(n)); }
@@ -142,8 +141,8 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            // instruction descriptor: D f32, A/B bf16, both MN-major (bits 15, 16), N, M = 128
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(L.Nmma >> 3) << 17) | ((128u >> 4) << 24);
+            // instruction descriptor: D f32, A/B fp16 (format 0), both MN-major (bits 15, 16), N, M = 128
+            const uint32_t idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(L.Nmma >> 3) << 17) | ((128u >> 4) << 24);
             // descriptor high word: SBO = 1024 bytes (8 positions), version 1, 128-byte swizzle
             const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
             // B in shift mode: SBO = 256 bytes (8 positions of 32 bytes), 32-byte swizzle
@@ -208,8 +207,8 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
 // out[y*sy + x*sx + tapmap[t]] = sum over splits of scratch[split][tile][t][y][x];  block = 32 outputs x kRL split lanes
 template <int kRL>
 __global__ void __launch_bounds__(32 * kRL) wgrad_tc_reduce_kernel(const float* __restrict__ scratch, int nsplit, int cxtiles, int ntaps, int cy, int cx,
-                                                                   float* __restrict__ out, long long sy, long long sx, int t0, int t1, int t2,
-                                                                   int t3, int t4, int t5, int t6, int t7, int t8)
+                                                                   float* __restrict__ out, long long sy, long long sx, float unscale, int t0,
+                                                                   int t1, int t2, int t3, int t4, int t5, int t6, int t7, int t8)
 {
     const int tapmap[9] = {t0, t1, t2, t3, t4, t5, t6, t7, t8};
     __shared__ float sh[kRL][33];
@@ -234,11 +233,14 @@ __global__ void __launch_bounds__(32 * kRL) wgrad_tc_reduce_kernel(const float* 
         float r = 0.f;
 #pragma unroll
         for (int k = 0; k < kRL; ++k) r += sh[k][ox];
-        out[y * sy + xg * sx + tapmap[t]] = r;
+        out[y * sy + xg * sx + tapmap[t]] = r * unscale;
     }
 }
 
 }  // namespace
+
+// scratch[split][tile][tap][64][64]: at most num_sms() (split, tile) pairs, 9 taps
+size_t wgrad_tc_scratch_floats() { return (size_t)k::num_sms() * 9 * 4096; }
 
 void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
 {
@@ -335,9 +337,9 @@ void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch)
     while (cols < L.npairs * L.Nmma) cols *= 2;
     L.tmem_cols = cols;
     L.cxtiles = (job.cx + 63) / 64;
-    L.nsplit = (int)std::max<long long>(1, std::min<long long>(L.chunks, kMaxSplitTilesTc / L.cxtiles));
+    L.nsplit = (int)std::max<long long>(1, std::min<long long>(L.chunks, k::num_sms() / L.cxtiles));
     L.scratch = scratch;
-    L.out = job.out; L.sy = job.sy; L.sx = job.sx;
+    L.out = job.out; L.sy = job.sy; L.sx = job.sx; L.unscale = job.unscale;
     L.cy_real = job.cy_real ? job.cy_real : job.cy; L.cx_real = job.cx_real ? job.cx_real : job.cx;
     make_tensor_map_2d(&L.tmX, job.x, job.g.positions(), job.x_ctot, 64, L.seg_alloc);
     // shift mode: one [kw + 8][16] tile per run (32-byte rows, 32-byte swizzle); the three shifts are row offsets into it
@@ -359,7 +361,7 @@ void launch_wgrad_tc(const WgradTcLaunch& L, cudaStream_t st)
     const long long total = (long long)L.ntaps * L.cy_real * L.cx_real;
     static const int rl = getenv("AB_RL") ? atoi(getenv("AB_RL")) : 4;   // split lanes per 32 outputs: 4 measured best (2: 7.88, 4: 7.85, 8: 7.88, 16: 7.98, 32: 8.47 ms per step)
 #define AB_REDUCE(R) wgrad_tc_reduce_kernel<R><<<(unsigned)((total + 31) / 32), 32 * R, 0, st>>>(L.scratch, L.nsplit, L.cxtiles, L.ntaps, L.cy_real, L.cx_real, L.out, \
-        L.sy, L.sx, L.tapmap[0], L.tapmap[1], L.tapmap[2], L.tapmap[3], L.tapmap[4], L.tapmap[5], L.tapmap[6], L.tapmap[7], L.tapmap[8])
+        L.sy, L.sx, L.unscale, L.tapmap[0], L.tapmap[1], L.tapmap[2], L.tapmap[3], L.tapmap[4], L.tapmap[5], L.tapmap[6], L.tapmap[7], L.tapmap[8])
     if (rl == 2) AB_REDUCE(2); else if (rl == 16) AB_REDUCE(16); else if (rl == 8) AB_REDUCE(8); else AB_REDUCE(4);
 #undef AB_REDUCE
     k::count_launch(2);

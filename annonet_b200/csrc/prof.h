@@ -21,10 +21,10 @@ enum Family {
     F_BLEND,
     F_INPUT,         // to_tensor / tile extraction
     F_OPTIMIZER,
-    F_PACK,          // layout / precision conversion of the bf16 tensor-core path
+    F_PACK,          // layout / precision conversion of the h16 tensor-core path
     F_CONV_TC,       // tcgen05 implicit-GEMM convolutions (forward, backward-data)
     F_WGRAD_TC,      // tcgen05 filter gradients
-    F_EW_BF16,       // bf16 NHWC elementwise / reduction kernels (bn, mish, pool, bias gradient)
+    F_EW_BF16,       // h16 NHWC elementwise / reduction kernels (bn, mish, pool, bias gradient)
     F_COUNT
 };
 

@@ -1,8 +1,17 @@
-// bf16 tensor-core path (AB_PRECISION_BF16): tcgen05 / TMEM / TMA implicit-GEMM convolutions and the
-// bf16 NHWC kernels around them.
+// Tensor-core path (AB_PRECISION_F16): tcgen05 / TMEM / TMA implicit-GEMM convolutions (kind::f16, fp16 operands, fp32
+// accumulation in TMEM) and the fp16 NHWC kernels around them.
+//
+// Why fp16 and not bf16: the net's 42 stacked batch norms amplify a forward rounding error of relative size e into a
+// parameter-gradient error of ~100 e at the deepest layers (measured and reproduced on the CPU by
+// experiments/bf16_emulation.py; DESIGN.md "Precision").  bf16 storage (e = 2^-9) leaves those gradients 20-35 % off, fp16
+// storage alone 3-8 %.  The TRAINING forward pass therefore keeps every activation as a PAIR of fp16 values (hi + lo, 22
+// significant bits) and every filter as a pair as well, and the forward convolutions run three MMAs per K chunk
+// (A_hi W_hi + A_lo W_hi + A_hi W_lo) -- the tensor pipe has the headroom, the layers are HBM / epilogue bound.  The
+// backward pass (gradients, filter gradients) and inference use single fp16 values; gradients are multiplied by a
+// power-of-two loss scale so that they sit in fp16's normal range.
 //
 // Activation layout ("padded flat NHWC"): a tensor of N samples, H x W pixels, C channels is stored as
-//     bf16 [N*S + P + 1 positions][C],   P = W + 1,  S = (H + 1) * P,
+//     h16 [N*S + P + 1 positions][C],   P = W + 1,  S = (H + 1) * P,
 //     position(n, y, x) = n*S + (y + 1)*P + (x + 1),
 // i.e. every sample carries one zero row above it and every row one zero pixel to its left.  The pad to
 // the right of a row is the left pad of the next row, the pad below a sample is the top pad of the next
@@ -14,14 +23,14 @@
 // measured with experiments/umma_probe.cu -- so any row offset is legal).
 #pragma once
 #include <cuda.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 
 namespace ab {
 namespace tc {
 
-typedef __nv_bfloat16 bf16;
+typedef __half h16;
 
 struct Geo {            // geometry of one padded flat tensor
     int N = 0, H = 0, W = 0;
@@ -49,6 +58,11 @@ struct ConvLaunch {
     alignas(64) CUtensorMap tmB;  // packed filters [tap][npad_total][padded K], box {kc, nblk}
     int a_c0 = 0;                 // first channel of the input slice
     int nchunks = 0, kc = 16;     // K = nchunks * kc channels per tap (filters zero-padded beyond the real Cin)
+    // Split operands (training forward): nchunks = 3 * nch1.  Chunk c of part p reads the A box at channel a_c0 + c*kc, row
+    // offset (p == 1 ? a_lo_rows : 0) -- the lo halves live a_lo_rows positions behind the hi halves in the same allocation --
+    // and the B box at K coordinate p*kpart + c*kc of the pack [W_hi | W_hi | W_lo].  Unsplit: nch1 = nchunks.
+    int nch1 = 0, kpart = 0;
+    long long a_lo_rows = 0;
     int ntaps = 0;
     // Tiling of the positions.  The tensor is a 2-D array of [N*(H+1) rows][P columns]; a CTA owns `th` M tiles of
     // 128 positions: FLAT: consecutive runs (tile m starts at o0 + 128*m), one merged halo segment;
@@ -78,8 +92,9 @@ struct ConvLaunch {
     long long S = 0; int P = 0, H = 0, W = 0, Nsamples = 0;
     int mode = OUT_BF16, act = ACT_NONE;
     int cout = 0;                 // real output channels (<= npad_total)
-    void* out = nullptr;          // bf16 [pos][out_ctot] or f32 planes
+    void* out = nullptr;          // h16 [pos][out_ctot] or f32 planes
     int out_ctot = 0, out_c0 = 0;
+    long long out_lo_off = 0;     // OUT_BF16 / OUT_BF16_UP: also store the rounding residual (lo half) this many ELEMENTS behind; 0: none
     long long out_S = 0; int out_P = 0;  // fine grid (OUT_BF16_UP*)
     int par_a = 0, par_b = 0;     // parity class of OUT_BF16_UP*
     const float* bias = nullptr;  // [cout] or null
@@ -93,13 +108,15 @@ struct ConvLaunch {
     double flops = 0, bytes = 0;  // algorithmic work (for the profiler)
 };
 
-// host: fill tmA/tmB and the derived tiling fields.  src: bf16 [src_positions][src_ctot].
+// host: fill tmA/tmB and the derived tiling fields.  src: h16 [src_positions][src_ctot].
 struct ConvSetup {
-    const bf16* src = nullptr; long long src_positions = 0; int src_ctot = 0, a_c0 = 0, cin = 0;
-    const bf16* packed = nullptr;  // packed filters (see pack_filters_bf16)
+    const h16* src = nullptr; long long src_positions = 0; int src_ctot = 0, a_c0 = 0, cin = 0;
+    const h16* packed = nullptr;  // packed filters (see pack_filters_bf16)
     int ntaps = 0; int tap_dy[9] = {0}, tap_dx[9] = {0};  // tap offset = dy*P + dx on the M grid
     int npad_total = 0;
     Geo grid;                      // geometry the M tiles walk over (the source tensor's)
+    // split operands: src holds 2 * src_positions rows (hi halves, then lo halves) and `packed` three K parts of padded_k(cin)
+    int split = 0;
 };
 int padded_k(int cin);             // multiple of 64
 int padded_n(int cout);            // multiple of 16
@@ -109,25 +126,29 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s);
 void launch_conv(const ConvLaunch& L, cudaStream_t st, int rev = 0);
 
 // packed[tap][n][k] = (n < nreal && k < kreal) ? w[n*sn + k*sk + tapmap[tap]] : 0,   n < npad_total, k < padded_k(kreal)
-void pack_filters_bf16(const float* w, bf16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
+void pack_filters_bf16(const float* w, h16* packed, int nreal, int npad_total, int kreal, int ntaps, const int* tapmap, long long sn,
                        long long sk, cudaStream_t st);
 
-// ---- bf16 NHWC kernels around the convolutions (kernels_nhwc.cu) ---------------------------------
+// ---- h16 NHWC kernels around the convolutions (kernels_nhwc.cu) ---------------------------------
 // input_rgb_image::to_tensor (input.h:68-117) [+ tile extraction with clamp-to-edge, annonet_infer.cpp:68-75]:
 // u8 HWC images [N][IH][IW][3] -> padded flat NHWC with 8 channels (3 real + 5 zero); out pixel (y, x) of sample n
 // reads image pixel (clamp(top + y), clamp(left + x)).
-void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, bf16* out, const Geo& g, float ar, float ag, float ab_,
-                   cudaStream_t st);
+// lo_off != 0: the rounding residual of every value goes to out[lo_off + ...] (the lo half of a split tensor)
+void image_to_nhwc(const uint8_t* img, int IH, int IW, int left, int top, h16* out, const Geo& g, float ar, float ag, float ab_,
+                   cudaStream_t st, long long lo_off = 0);
 // max_pool_<3,3,2,2,0,0> (cpu_dlib.cpp:1888-1943): channels [c0, c0 + C) of `in` (geometry gi, ctot channels) -> dense
 // pooled tensor [positions of go][C]
 // arg (optional, training): u8 [positions of go][C], the index (r*3 + q) of the window element that won
-void maxpool_nhwc(const bf16* in, int in_ctot, int c0, int C, const Geo& gi, bf16* out, const Geo& go, cudaStream_t st, uint8_t* arg = nullptr);
+// in_lo_off / out_lo_off != 0: split tensors -- the maximum is taken over hi + lo and both halves are written
+void maxpool_nhwc(const h16* in, int in_ctot, int c0, int C, const Geo& gi, h16* out, const Geo& go, cudaStream_t st, uint8_t* arg = nullptr,
+                  long long in_lo_off = 0, long long out_lo_off = 0);
 
-// ---- training-side bf16 NHWC kernels (kernels_train_nhwc.cu) ------------------------------------
+// ---- training-side h16 NHWC kernels (kernels_train_nhwc.cu) ------------------------------------
 // A "view" = channels [c0, c0 + C) of a padded flat tensor with ctot channels per position.
 struct View {
-    bf16* p = nullptr;
+    h16* p = nullptr;
     int ctot = 0, c0 = 0, C = 0;
+    long long lo_off = 0;   // split tensors: element offset of the lo half (0: single fp16 values)
 };
 struct ViewF {   // same, fp32 elements (the conv outputs z that feed a batch norm stay fp32: normalisation amplifies rounding)
     float* p = nullptr;
@@ -152,47 +173,49 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
 // backward pass 1 (cpu_dlib.cpp:1228-1250): red[c] = sum dv, red[C + c] = sum dv*xhat
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
                              const float* beta, const float* stats, double* red, cudaStream_t st, int rev = 0);
-// backward pass 2 (cpu_dlib.cpp:1252-1288): dz = gradient at the conv output (bf16, pads untouched), dgamma/dbeta from `red`,
-// dbias[c] = sum dz (assign_conv_bias_gradient, cpu_dlib.cpp:470-504; dbias must be zeroed by the caller)
+// backward pass 2 (cpu_dlib.cpp:1252-1288): dz = gradient at the conv output (h16, pads untouched), dgamma/dbeta from `red`,
+// dbias[c] = sum dz (assign_conv_bias_gradient, cpu_dlib.cpp:470-504; dbias must be zeroed by the caller).  gy and dz carry
+// the loss scale; the three parameter gradients are multiplied by `unscale` = 1 / loss scale
 void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, const Geo& g, int mish_first, int has_mish, const float* gamma,
                             const float* beta, const float* stats, const double* red, float* dgamma, float* dbeta, float* dbias,
-                            cudaStream_t st, int rev = 0);
-// g[c] += sum over positions of v (caller zeroes g)
-void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st);
+                            cudaStream_t st, int rev = 0, float unscale = 1.f);
+// g[c] += unscale * sum over positions of v (caller zeroes g)
+void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st, float unscale = 1.f);
 // max_pool_<3,3,2,2,0,0> gradient (cpu_dlib.cpp:1971-2017): the first maximum of a window in row-major order receives it; gin +=
 // (`arg` as written by maxpool_nhwc in the forward pass)
-void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const bf16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
-// f32 planes [N][K][H][W] -> bf16 padded flat [positions][8] (channels >= K are zero)
-void planes_to_nhwc8(const float* planes, int K, bf16* out, const Geo& g, cudaStream_t st);
+void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
+// f32 planes [N][K][H][W] * scale -> h16 padded flat [positions][8] (channels >= K are zero)
+void planes_to_nhwc8(const float* planes, int K, h16* out, const Geo& g, cudaStream_t st, float scale = 1.f);
 // out (fine geometry, dense [positions][C]) = zero-stuffed in: out[2i][2j] = in[i][j], 0 at the other pixels
-void upsample_zero_nhwc(const View& in, const Geo& gc, bf16* out, const Geo& gf, cudaStream_t st);
+void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, cudaStream_t st);
 
 // one filter-pack job of pack_filters_batched: same element mapping as pack_filters_bf16
 struct PackJob {
-    long long w_off, packed_off;   // floats into the arena, bf16 elements into the pack buffer
+    long long w_off, packed_off;   // floats into the arena, h16 elements into the pack buffer
     long long sn, sk;
     int nreal, npad, kreal, kp, ntaps;
     int tapmap[9];
+    int parts;                     // 1: [tap][n][kp] of fp16(w);  3: [tap][n][3*kp] = [hi | hi | lo], hi = fp16(w), lo = fp16(w - hi)
 };
-void pack_filters_batched(const float* arena, bf16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st);
+void pack_filters_batched(const float* arena, h16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st);
 
-// ---- filter gradients on the tensor cores (kernels_wgrad_mma.cu) ----------------------------------
+// ---- filter gradients on the tensor cores (kernels_wgrad_tc.cu) -----------------------------------
 //   G[tap][y][x] = sum_pos DY[pos][dy_c0 + y] * X[pos + tap_dy*P + tap_dx][x_c0 + x]      y < cy <= 64, x < cx
 // over ALL positions of geometry g (pads of both tensors are zero), scattered to out[y*sy + x*sx + tapmap[tap]].
 struct WgradJob {
-    const bf16* dy = nullptr; int dy_ctot = 0, dy_c0 = 0, cy = 0;   // cy, cx: loaded channels (multiples of 8)
-    const bf16* x = nullptr;  int x_ctot = 0, x_c0 = 0, cx = 0;
+    const h16* dy = nullptr; int dy_ctot = 0, dy_c0 = 0, cy = 0;   // cy, cx: loaded channels (multiples of 8)
+    const h16* x = nullptr;  int x_ctot = 0, x_c0 = 0, cx = 0;
     int cy_real = 0, cx_real = 0;                                    // channels written to `out` (<= cy, cx)
     Geo g;
     int ntaps = 0, tap_dy[9] = {0}, tap_dx[9] = {0}, tapmap[9] = {0};
     float* out = nullptr; long long sy = 0, sx = 0;
+    float unscale = 1.f;            // out = unscale * G (1 / loss scale)
 };
-// bf16 [rows][ctot] tensor, box {box_ch (16 / 32 / 64: 32 / 64 / 128-byte swizzle), box_rows}
+// h16 [rows][ctot] tensor, box {box_ch (16 / 32 / 64: 32 / 64 / 128-byte swizzle), box_rows}
 void make_tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int box_ch, int box_rows);
-size_t wgrad_mma_scratch_floats();
-void wgrad_mma(const WgradJob& job, float* scratch, cudaStream_t st);
+size_t wgrad_tc_scratch_floats();
 
-// The same GEMM on tcgen05 (kernels_wgrad_tc.cu): MN-major shared-memory descriptors over TMA-staged [position][64 channel]
+// tcgen05 (kernels_wgrad_tc.cu): MN-major shared-memory descriptors over TMA-staged [position][64 channel]
 // tiles, two taps fused into one M = 128 MMA through the descriptor's leading-dimension offset, accumulators in TMEM.
 struct WgradTcLaunch {
     alignas(64) CUtensorMap tmX, tmY;
@@ -218,6 +241,7 @@ struct WgradTcLaunch {
     float* scratch = nullptr;
     // reduction + scatter (same as WgradJob)
     float* out = nullptr; long long sy = 0, sx = 0; int tapmap[9] = {0}; int cy_real = 0, cx_real = 0;
+    float unscale = 1.f;
     double flops = 0, bytes = 0;
 };
 void setup_wgrad_tc(WgradTcLaunch& L, const WgradJob& job, float* scratch);

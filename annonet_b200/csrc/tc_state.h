@@ -1,5 +1,5 @@
-// State of the bf16 tensor-core path of one Engine (AB_PRECISION_BF16): padded flat NHWC workspaces,
-// bf16 filter packs and the prepared launch descriptors (tensor maps) of every conv group.
+// State of the fp16 tensor-core path of one Engine (AB_PRECISION_F16): padded flat NHWC workspaces,
+// fp16 filter packs and the prepared launch descriptors (tensor maps) of every conv group.
 #pragma once
 #include "engine.h"
 #include "tc.h"
@@ -16,6 +16,7 @@ struct TcGroup {
     int fwd_tapdy[4][9] = {}, fwd_tapdx[4][9] = {};  // tap offset = dy*P + dx of the M grid
     int nlaunch = 1;
     int npad = 0;
+    size_t train_pack_off[4] = {0, 0, 0, 0};   // training forward: split packs [hi | hi | lo] (3 x the K extent), own buffer
     std::vector<tc::ConvLaunch> infer;   // prepared for the current inference geometry
     // training
     std::vector<tc::ConvLaunch> fwd;     // conv -> z (or destination)
@@ -30,26 +31,31 @@ struct TcGroup {
 
 struct TcWorkspace {
     int n = 0, h = 0, w = 0;
+    // split (training activations): every tensor is stored twice, hi halves then lo halves (tc.h); the lo half of a level / the
+    // image starts level_lo[l] / img_lo elements behind the hi half
+    bool split = false;
     tc::Geo geo[8];
-    DevBuf level[8];           // bf16 [positions][level_channels]
-    DevBuf img;                // bf16 [positions][8]
+    DevBuf level[8];           // h16 [positions][level_channels]  (x 2 when split)
+    DevBuf img;                // h16 [positions][8]
     DevBuf pool;               // pooled inputs of the transition_down groups, dense
+    long long level_lo[8] = {0}, img_lo = 0;   // (a pooled tensor's lo half: positions * cin elements behind its hi half)
     DevBuf pool_arg;           // training: u8 index of the winning window element, same element offsets as `pool`
     std::vector<size_t> pool_off;  // per group, in elements
 };
 
 struct TcState {
     std::vector<TcGroup> groups;
-    DevBuf fwd_packs, bwd_packs;
+    DevBuf fwd_packs, bwd_packs, train_packs;
     bool fwd_packs_valid = false, bwd_packs_valid = false;
+    float loss_scale = 1.f;    // power of two folded into the loss gradient; parameter gradients are divided by it again
     TcWorkspace iw;            // inference
     // training
     TcWorkspace tw, tg;        // activations / gradients
     DevBuf z;                  // per bn group: conv output z, fp32 [positions][cout]
-    DevBuf dz;                 // per bn group: gradient at the conv output, bf16 [positions][cout] (same element offsets as z)
+    DevBuf dz;                 // per bn group: gradient at the conv output, h16 [positions][cout] (same element offsets as z)
     DevBuf dpool;              // per transition_down group: gradient at the pooled tensor              [positions][cin]
     DevBuf upx;                // per `up` group: zero-stuffed input on the fine grid (filter gradient)  [positions][cin]
-    DevBuf glogits16;          // loss gradient as bf16 [positions][8]
+    DevBuf glogits16;          // loss gradient as h16 [positions][8]
     DevBuf sums, bias_tmp, wscratch, pack_jobs;
     int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
     bool train_ready = false;
@@ -57,13 +63,13 @@ struct TcState {
     // CUDA graph of one whole training step (static shapes and pointers): replayed while the key stays the same
     struct GraphKey {
         const void* imgs = nullptr; const void* labels = nullptr;
-        int n = 0, h = 0, w = 0, update = 0, skip_dead = 0;
-        double lr = 0, wd = 0, momentum = 0;
+        int n = 0, h = 0, w = 0, update = 0, skip_dead = 0, world = 1, solver = 0;
+        double lr = 0, wd = 0, momentum = 0, loss_scale = 0;
         unsigned long long window = 0;
         bool operator==(const GraphKey& o) const
         {
             return imgs == o.imgs && labels == o.labels && n == o.n && h == o.h && w == o.w && update == o.update && skip_dead == o.skip_dead &&
-                   lr == o.lr && wd == o.wd && momentum == o.momentum && window == o.window;
+                   world == o.world && solver == o.solver && loss_scale == o.loss_scale && lr == o.lr && wd == o.wd && momentum == o.momentum && window == o.window;
         }
     };
     GraphKey graph_key, seen_key;
@@ -78,9 +84,11 @@ struct TcState {
 };
 
 // prepared launches of one conv group in the forward direction (engine_bf16.cu)
-void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const tc::bf16* packs,
-                            const float* P, std::vector<tc::ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0, int mode, int act);
-void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, cudaStream_t st);
+// packs / pack_off: the group's filter packs (split packs when ws.split); dst_lo_off: element offset of the destination's lo half
+void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const tc::h16* packs,
+                            const size_t* pack_off, const float* P, std::vector<tc::ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0,
+                            long long dst_lo_off, int mode, int act);
+void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, bool split, cudaStream_t st);
 
 
 }  // namespace ab

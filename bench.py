@@ -202,7 +202,7 @@ def own_arm(args):
     clocks = ClockSampler(local).start()   # long before the timed region (nvidia-smi start-up)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    precision = ab.AB_PRECISION_BF16 if args.precision == "bf16" else ab.AB_PRECISION_FP32
+    precision = ab.AB_PRECISION_F16 if args.precision == "bf16" else ab.AB_PRECISION_FP32
 
     net = ab.TrainingNet(local, precision)
     net.Initialize(CLASSES, 1.0, 1, seed=1)         # identical weights on every rank (same seed)

@@ -33,7 +33,9 @@ typedef enum {
 /* precision of activations/weights inside the convolutions; accumulation is always fp32 */
 typedef enum {
     AB_PRECISION_FP32 = 0, /* fp32 FMA path: logits within 1e-4 relative of the dlib CPU build */
-    AB_PRECISION_BF16 = 1  /* bf16 tcgen05 path: within 2e-2                                    */
+    AB_PRECISION_F16 = 1   /* fp16 tcgen05 path (fp32 accumulate; training forward on hi + lo  */
+                           /* fp16 pairs): the north star's 2e-2 "bf16 path" tolerance -- bf16 */
+                           /* storage cannot meet it on this net (DESIGN.md "Precision")       */
 } ab_precision;
 
 /* dlib::loss_multiclass_log_per_pixel_weighted_::weighted_label<uint16_t>
@@ -70,7 +72,8 @@ typedef enum {
     AB_HYPER_SOLVER = 6,                 /* 0 = sgd (compiled-in default), 1 = adam (NetPimpl.h:17-23)        */
     AB_HYPER_ADAM_BETA1 = 7,
     AB_HYPER_ADAM_BETA2 = 8,
-    AB_HYPER_SKIP_DEAD_LAYERS = 9        /* 1: do not run the 7 never-consumed dense layers in training        */
+    AB_HYPER_SKIP_DEAD_LAYERS = 9,       /* 1: do not run the 7 never-consumed dense layers in training        */
+    AB_HYPER_LOSS_SCALE = 10             /* fp16 path: power of two the loss gradient is multiplied by (0: auto) */
 } ab_hyper_id;
 
 /* ---- library ------------------------------------------------------------------------------ */

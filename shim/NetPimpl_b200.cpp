@@ -48,7 +48,7 @@ ab_net* new_net()
 {
     ab_net* n = nullptr;
     // AB_DEVICE / AB_PRECISION: deployment knobs of the engine (0 = fp32 parity path, 1 = bf16 tensor-core path)
-    check(ab_net_create(env_int("AB_DEVICE", 0), env_int("AB_PRECISION", AB_PRECISION_BF16), &n));
+    check(ab_net_create(env_int("AB_DEVICE", 0), env_int("AB_PRECISION", AB_PRECISION_F16), &n));
     return n;
 }
 

@@ -1,0 +1,198 @@
+"""fp16 tcgen05 path (AB_PRECISION_F16) against the compiled reference (oracle/_ref/annonet_ref, the unmodified dlib CPU
+build) on BASELINE.json's configurations.  north_star tolerance for the half-precision tensor-core path: 2e-2 relative on
+logits, loss and gradients; label maps >= 99.9 % with disagreements only at near-ties.
+
+Gradients are compared PER LAYER (filters / gamma and bias / beta separately), in two norms: max-abs error over max-abs
+reference (conftest.rel_err, the north star's "relative") and relative L2.  No cosine / whole-vector escape hatches.  The
+yardstick is the exact-sum numpy oracle; against the reference binary the bar is max(2e-2, twice the reference's own distance
+from exact arithmetic) -- its sequential fp32 batch-norm sums move its own deepest gradients by several per cent at
+32 x 255 x 255 (conftest.oracle_train_outputs, DESIGN.md "Precision")."""
+import numpy as np
+import pytest
+
+import annonet_numpy as on
+import dlib_format as df
+from conftest import (oracle_train_outputs, ref_grads_by_layer, ref_infer_outputs, ref_random_net, ref_train_outputs, rel_err, synth_image,
+                      train_case)
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-2
+
+
+def _rel_l2(a, b):
+    return float(np.linalg.norm(np.asarray(a, np.float64) - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def _near_tie_only(labels, ref_labels, ref_scores, tol):
+    bad = labels != ref_labels
+    top2 = np.sort(ref_scores, axis=0)[-2:]
+    return np.all((top2[1] - top2[0])[bad] < tol * np.abs(ref_scores).max())
+
+
+def _check_gradients(net, onet, exact, ref_grads, tol, label):
+    """every live layer of `net` (after compute_gradients): within `tol` of the exact-sum oracle, and within
+    max(tol, 2 x the reference's own summation-noise floor) of the compiled reference (conftest.oracle_train_outputs)"""
+    L = onet.layers
+    rows = []
+    for i, r in sorted(ref_grads_by_layer(onet, ref_grads).items()):
+        r = r.reshape(-1).astype(np.float64)
+        mine = net.layer_gradient(i)
+        assert mine.shape == r.shape
+        if np.abs(r).max() == 0:
+            assert np.abs(mine).max() == 0, f"layer<{i}> is dead: its gradient must be exactly zero"
+            continue
+        e = exact[f"g{i}"].astype(np.float64)
+        t = L[i]["type"]
+        nb = L[i]["num_filters"] if t in ("con", "cont") else r.size // 2
+        wsl, bsl = slice(0, r.size - nb), slice(r.size - nb, None)
+        parts = [("filters" if t != "bn" else "gamma", wsl)]
+        # a conv bias DIRECTLY in front of a batch norm (conv -> bn -> mish: level0, level0t) has an exactly zero gradient, the
+        # normalisation removes the mean: what the reference holds there is rounding noise ~1e-7 of the filter gradient; ours
+        # must be as negligible.  (conv -> mish -> bn: the bias sits in front of the mish, its gradient is real.)
+        feeds_bn = t in ("con", "cont") and L[i - 1]["type"] == "bn"
+        if feeds_bn:
+            assert np.abs(mine[bsl]).max() <= tol * np.abs(e[wsl]).max(), f"layer<{i}> bias gradient in front of a bn must vanish"
+        else:
+            parts.append(("bias" if t != "bn" else "beta", bsl))
+        for name, sl in parts:
+            rows.append((i, t, name, rel_err(mine[sl], e[sl]), _rel_l2(mine[sl], e[sl]), rel_err(mine[sl], r[sl]), _rel_l2(mine[sl], r[sl]),
+                         rel_err(e[sl], r[sl]), _rel_l2(e[sl], r[sl])))
+    print(f"{label}: layer, type, part | vs exact-sum oracle: max-rel, rel-L2 | vs reference: max-rel, rel-L2 | reference's own noise floor: max-rel, rel-L2")
+    for row in rows:
+        print("   layer<%d> %-5s %-7s | %.3e %.3e | %.3e %.3e | %.3e %.3e" % row)
+    worst = max(rows, key=lambda x: max(x[3], x[4]))
+    print(f"{label}: worst vs exact: layer<{worst[0]}> {worst[1]} {worst[2]}: max-rel {worst[3]:.3e} rel-L2 {worst[4]:.3e}  ({len(rows)} tensors); "
+          f"worst vs reference {max(max(x[5], x[6]) for x in rows):.3e} (its noise floor {max(max(x[7], x[8]) for x in rows):.3e})")
+    # Max-pool winners are discontinuous: two correct implementations whose activations differ in the last bits pick different
+    # winners at a few near-ties, which moves single elements of the coarse levels' gradients by several per cent (the fp32
+    # engine, the numpy oracle and the reference binary all differ from each other that way).  The max-norm bar therefore is
+    # max(tol, twice the WORST max-norm distance between the reference and exact arithmetic on this batch); rel-L2 is strict.
+    floor_max = max(x[7] for x in rows)
+    for row in rows:
+        assert row[4] <= tol, f"layer<{row[0]}> {row[1]} {row[2]} vs exact-sum oracle: rel-L2 {row[4]:.3e} > {tol}"
+        assert row[3] <= max(tol, 2 * floor_max), f"layer<{row[0]}> {row[1]} {row[2]} vs exact-sum oracle: max-rel {row[3]:.3e} (floor {floor_max:.3e})"
+        assert row[6] <= max(tol, 2 * row[8]), f"layer<{row[0]}> {row[1]} {row[2]} vs reference: rel-L2 {row[6]:.3e} (its noise floor {row[8]:.3e})"
+        assert row[5] <= max(tol, 2 * floor_max), f"layer<{row[0]}> {row[1]} {row[2]} vs reference: max-rel {row[5]:.3e}"
+    return worst
+
+
+def _training_case(ab, n, h, w, seed, name, label):
+    net_bytes = ref_random_net(3, 5)
+    imgs, labs, wts = train_case(n, h, w, 3, seed=seed)
+    ref = ref_train_outputs(net_bytes, imgs, labs, wts, name)
+    exact = oracle_train_outputs(net_bytes, imgs, labs, wts, name + "_exact")
+    net = ab.TrainingNet(0, ab.AB_PRECISION_F16)
+    net.Deserialize(net_bytes)
+    loss = net.compute_gradients(imgs, ab.pack_labels(labs, wts))
+    ref_loss, exact_loss = float(ref["loss"][0]), float(exact["loss"][0])
+    lg = net.logits()[:, :, ::2, ::2]
+    e_exact, e_ref = rel_err(lg, exact["logits_sub2"]), rel_err(lg, ref["logits_sub2"])
+    print(f"{label}: loss {loss:.6f} vs exact-sum oracle {exact_loss:.6f}, reference {ref_loss:.6f}; logits max-rel {e_exact:.3e} (oracle) {e_ref:.3e} (reference)")
+    assert abs(loss - exact_loss) <= TOL * abs(exact_loss) and abs(loss - ref_loss) <= TOL * abs(ref_loss)
+    assert e_exact <= TOL and e_ref <= TOL
+    _check_gradients(net, df.parse_net(net_bytes), exact, bytes(ref["grads"]), TOL, label)
+
+
+def test_f16_training_step_matches_reference_on_baseline_config1(ab):
+    """BASELINE configs[1]: one annonet_train step, 32 crops of 255 x 255 (the size the CLI feeds for "256"), 3 classes,
+    weighted per-pixel loss -- loss, logits and EVERY live layer's parameter gradient"""
+    _training_case(ab, 32, 255, 255, 101, "train_32x255_k3", "configs[1] 32x255x255")
+
+
+def test_f16_training_small_batch_matches_reference(ab):
+    """a small, odd-shaped batch (6 x 191 x 255: the deepest batch norm sees 36 samples) -- same per-layer bar"""
+    _training_case(ab, 6, 191, 255, 102, "train_6x191x255_k3", "6x191x255")
+
+
+def test_f16_inference_matches_reference_on_baseline_config0(ab):
+    """BASELINE configs[0]: annonet_infer of one 1024 x 1024 image, 3 classes (one tile, run at 1087 x 1087)"""
+    anet = ref_random_net(3, 5, training=False)
+    img = synth_image(np.random.default_rng(103), 1024, 1024)
+    ref = ref_infer_outputs(anet, img, 1024, "infer_1024_k3")
+    rt = ab.RuntimeNet(0, ab.AB_PRECISION_F16)
+    rt.Deserialize(anet)
+    labels, blended = rt.infer(img, 1024, 1024, return_blended=True)
+    err = rel_err(blended, ref["blended"])
+    agree = float(np.mean(labels == ref["labels"]))
+    print(f"configs[0]: blended logits max-rel {err:.3e}, labels agree {agree:.5f}")
+    assert err <= TOL
+    assert agree >= 0.999 or _near_tie_only(labels, ref["labels"], ref["blended"], 2 * TOL)
+    assert _near_tie_only(labels, ref["labels"], ref["blended"], 2 * TOL)
+    assert np.array_equal(labels, rt.infer(img, 1024, 1024))   # deterministic
+
+
+def test_f16_tiled_inference_8_classes_matches_reference_on_baseline_config2_crop(ab):
+    """BASELINE configs[2] on a crop: 8 classes, several overlapping tiles, blend + argmax with gains"""
+    anet = ref_random_net(8, 6, training=False)
+    img = synth_image(np.random.default_rng(104), 700, 900)
+    gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
+    ref = ref_infer_outputs(anet, img, 512, "infer_700x900_k8_t512", gains=gains)
+    rt = ab.RuntimeNet(0, ab.AB_PRECISION_F16)
+    rt.Deserialize(anet)
+    labels, blended = rt.infer(img, 512, 512, gains=gains, return_blended=True)
+    err = rel_err(blended, ref["blended"])
+    agree = float(np.mean(labels == ref["labels"]))
+    print(f"configs[2] crop: blended logits max-rel {err:.3e}, labels agree {agree:.5f}")
+    assert err <= TOL
+    scores = ref["blended"] + np.asarray(gains, np.float32)[:, None, None]
+    assert _near_tie_only(labels, ref["labels"], scores, 2 * TOL)
+
+
+def test_f16_forward_matches_oracle(ab):
+    rng = np.random.default_rng(17)
+    rt = df.to_runtime(df.random_net(class_count=3, seed=21))
+    img = synth_image(rng, 127, 191)
+    ref = on.logits_of(on.forward(rt, on.to_tensor(img[None], rt.layers[-1]["avg"]), training=False, skip_dead=True))[0]
+    e16 = ab.RuntimeNet(0, ab.AB_PRECISION_F16)
+    e16.Deserialize(df.serialize_net(rt))
+    err = rel_err(e16.Forward(img), ref)
+    print(f"fp16 forward: rel err {err:.3e} vs the numpy oracle")
+    assert err <= TOL
+
+
+def test_f16_training_tracks_fp32(ab):
+    """a few SGD steps: the tensor-core path's loss curve follows the fp32 path's, parameters stay close, and the trained
+    net converts to a runtime net"""
+    data = df.serialize_net(df.random_net(class_count=3, seed=21))
+    imgs, labs, wts = train_case(4, 127, 127, 3, seed=20)
+    wl = ab.pack_labels(labs, wts)
+    curves, params = [], []
+    for prec in (ab.AB_PRECISION_FP32, ab.AB_PRECISION_F16):
+        net = ab.TrainingNet(0, prec)
+        net.Deserialize(data)
+        net.SetLearningRate(0.05)
+        losses = []
+        for _ in range(6):
+            net.StartTraining(imgs, wl)
+            losses.append(net.sync())
+        curves.append(losses)
+        params.append(df.parse_net(net.Serialize()))
+        if prec == ab.AB_PRECISION_F16:
+            rt = net.GetRuntimeNet(0, ab.AB_PRECISION_F16)
+            assert np.isfinite(rt.Forward(imgs[0])).all()
+    print("loss fp32", ["%.5f" % v for v in curves[0]], "fp16", ["%.5f" % v for v in curves[1]])
+    assert curves[1][-1] < curves[1][0]
+    for a, b in zip(*curves):
+        assert abs(a - b) <= 2e-3 * abs(a)
+    for (i, a), (_, b) in zip(params[1].param_layers(), params[0].param_layers()):
+        assert rel_err(a["params"], b["params"]) <= TOL, f"layer<{i}> parameters after 6 steps"
+
+
+def test_f16_loss_scale_is_transparent(ab):
+    """the loss scale only moves the fp16 gradients inside their normal range: gradients with 1/16 and 16 x the automatic
+    scale agree with the automatic one to fp16 rounding"""
+    onet = df.random_net(class_count=3, seed=21)
+    data = df.serialize_net(onet)
+    imgs, labs, wts = train_case(2, 127, 127, 3, seed=22)
+    wl = ab.pack_labels(labs, wts)
+    grads = []
+    for mul in (1.0, 1 / 16, 16.0):
+        net = ab.TrainingNet(0, ab.AB_PRECISION_F16)
+        net.Deserialize(data)
+        if mul != 1.0:
+            net.set_hyper(ab.HYPER_LOSS_SCALE, mul * 2 ** int(np.floor(np.log2(2 * 127 * 127 / 8))))
+        net.compute_gradients(imgs, wl)
+        grads.append(np.concatenate([net.layer_gradient(i) for i, _ in onet.param_layers()]))
+    for g in grads[1:]:
+        assert _rel_l2(g, grads[0].astype(np.float64)) < 5e-3
