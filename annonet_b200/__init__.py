@@ -57,7 +57,7 @@ EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
-    "ab_infer_tiled_partial", "ab_infer_finish", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
+"ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
@@ -260,15 +260,9 @@ class RuntimeNet(_Net):
         _check(lib.ab_infer_tiled_device(self._h, C.c_void_p(image_ptr), h, w, max_tile_w, max_tile_h, None, 0, C.c_void_p(labels_ptr)))
 
 
-    def infer_partial_device(self, image_ptr: int, h: int, w: int, max_tile_w: int, max_tile_h: int, rank: int, world: int):
-        """this rank's tile rows blended into its private canvas; returns (device pointer, floats) of the canvas
-        for the caller's all-reduce."""
-        canvas, n = C.c_void_p(), C.c_size_t()
-        _check(lib.ab_infer_tiled_partial(self._h, C.c_void_p(image_ptr), h, w, max_tile_w, max_tile_h, rank, world, C.byref(canvas), C.byref(n)))
-        return canvas.value, n.value
-
-    def infer_finish_device(self, h: int, w: int, labels_ptr: int) -> None:
-        _check(lib.ab_infer_finish(self._h, h, w, None, 0, C.c_void_p(labels_ptr)))
+    def comm_init(self, unique_id: bytes, rank: int, world: int) -> None:
+        """join an NCCL communicator: infer / infer_device then shard the tile rows over the ranks"""
+        _check(lib.ab_comm_init(self._h, unique_id, rank, world))
 
 
 class TrainingNet(_Net):

@@ -177,25 +177,8 @@ ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w
                                 int ngains, void* labels_dev)
 {
     return guarded([&] {
-        E(net).infer_tiled_device((const uint8_t*)image_dev, h, w, max_tile_w, max_tile_h, 0, 1);
-        E(net).infer_finish_device(h, w, gains, ngains, (uint16_t*)labels_dev);
+        E(net).infer_tiled_device((const uint8_t*)image_dev, h, w, max_tile_w, max_tile_h, gains, ngains, (uint16_t*)labels_dev);
     });
-}
-
-ab_status ab_infer_tiled_partial(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h, int rank, int world,
-                                 void** canvas_dev, size_t* canvas_floats)
-{
-    return guarded([&] {
-        ab::Engine& e = E(net);
-        e.infer_tiled_device((const uint8_t*)image_dev, h, w, max_tile_w, max_tile_h, rank, world);
-        if (canvas_dev) *canvas_dev = e.canvas();
-        if (canvas_floats) *canvas_floats = (size_t)e.plan().class_count * h * w;
-    });
-}
-
-ab_status ab_infer_finish(ab_net* net, int h, int w, const double* gains, int ngains, void* labels_dev)
-{
-    return guarded([&] { E(net).infer_finish_device(h, w, gains, ngains, (uint16_t*)labels_dev); });
 }
 
 ab_status ab_set_hyper(ab_net* net, int id, double v)

@@ -71,10 +71,10 @@ public:
     const float* forward_device(const uint8_t* img_dev, int h, int w);
     const float* forward_host(const uint8_t* img_host, int h, int w);
     void process_host(const uint8_t* img_host, int h, int w, const double* gains, int ngains, uint16_t* labels_host);
-    // annonet_infer(); image/labels on the device.  rank/world select tile rows (world = 1: all tiles)
-    void infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, int rank, int world);
-    void infer_finish_device(int h, int w, const double* gains, int ngains, uint16_t* labels_dev);
-    float* canvas() const { return canvas_.as<float>(); }
+    // annonet_infer(); image/labels on the device.  After comm_init the tile rows are sharded over the ranks as contiguous bands,
+    // seams are exchanged with the neighbours and every rank ends up with the whole label map (engine_infer.cu)
+    void infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
+                            uint16_t* labels_dev);
     void infer_tiled_host(const uint8_t* img_host, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                           uint16_t* labels_host, float* blended_host);
 
@@ -104,6 +104,7 @@ private:
     void forward_train(int n, int h, int w);
     void backward_train(int n, int h, int w);
     void optimizer_step();
+    void ensure_adam_state();
     void allreduce_range(size_t lo, size_t hi);
     k::Slice level_slice(Levels& L, int level, int c0, int C) const;
     // h16 tensor-core path (precision_ == AB_PRECISION_F16)
@@ -128,11 +129,14 @@ private:
     std::vector<size_t> running_off_;   // per group
     std::vector<unsigned long long> num_updates_, window_;  // per group; num_updates_ is a host mirror of nu_dev_ (load/snapshot)
     DevBuf nu_dev_;                     // per group: bn_ num_updates counter, advanced on the device by bn_finalize
-    unsigned long long adam_t_ = 0;
+    unsigned long long adam_t_ = 0;     // host mirror of the step count (the kernels read the device copy)
+    DevBuf adam_t_dev_;
+    int bucket_slot_ = 0;
 
     // inference workspace
     Levels iw_;
-    DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_;
+    DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_;
+    int canvas_rows_ = 0, canvas_row0_ = 0;   // the blend canvas holds image rows [canvas_row0_, canvas_row0_ + canvas_rows_)
     void* pinned_ = nullptr; size_t pinned_bytes_ = 0;
     void* pinned(size_t bytes);
 

@@ -1,4 +1,5 @@
 #include "engine.h"
+#include "nccl_api.h"
 #include "tc_state.h"
 
 #include <cstring>
@@ -31,31 +32,6 @@ void DevBuf::reserve(size_t n)
 }
 
 // ---- NCCL, resolved at run time from the process (torch bundles libnccl.so.2) -----------------
-struct NcclApi {
-    struct UniqueId { char internal[128]; };
-    void* lib = nullptr;
-    int (*GetUniqueId)(UniqueId*) = nullptr;
-    int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
-    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
-    int (*CommDestroy)(void*) = nullptr;
-    const char* (*GetErrorString)(int) = nullptr;
-    NcclApi()
-    {
-        lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
-        if (!lib) throw state_error(std::string("cannot load libnccl.so.2: ") + dlerror());
-        GetUniqueId = (decltype(GetUniqueId))dlsym(lib, "ncclGetUniqueId");
-        CommInitRank = (decltype(CommInitRank))dlsym(lib, "ncclCommInitRank");
-        AllReduce = (decltype(AllReduce))dlsym(lib, "ncclAllReduce");
-        CommDestroy = (decltype(CommDestroy))dlsym(lib, "ncclCommDestroy");
-        GetErrorString = (decltype(GetErrorString))dlsym(lib, "ncclGetErrorString");
-        if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy) throw state_error("libnccl lacks the expected symbols");
-    }
-    void check(int r, const char* what) const
-    {
-        if (r != 0) throw cuda_error(std::string("NCCL error in ") + what + ": " + (GetErrorString ? GetErrorString(r) : "?"));
-    }
-};
 
 void nccl_unique_id(void* id128)
 {
@@ -160,7 +136,7 @@ void Engine::load(const NetModel& m)
             }
         }
     }
-    params_.reserve(np * 4); grads_.reserve(np * 4); mom_.reserve(np * 4); lr_mul_.reserve(np * 4); wd_mul_.reserve(np * 4);
+    params_.reserve(np * 4); grads_.reserve((np + 1) * 4); mom_.reserve(np * 4);   // grads_[np]: the step loss of a data-parallel run lr_mul_.reserve(np * 4); wd_mul_.reserve(np * 4);
     running_.reserve(std::max<size_t>(roff, 1) * 4);
     AB_CUDA(cudaMemcpy(params_.p, hp.data(), np * 4, cudaMemcpyHostToDevice));
     AB_CUDA(cudaMemcpy(lr_mul_.p, lrm.data(), np * 4, cudaMemcpyHostToDevice));
@@ -241,6 +217,23 @@ void Engine::comm_init(const void* id128, int rank, int world)
     NcclApi::UniqueId id;
     std::memcpy(&id, id128, 128);
     nccl_->check(nccl_->CommInitRank(&comm_, world, id, rank), "ncclCommInitRank");
+    // a step captured before the communicator existed would replay without its all-reduces and without the 1/world factor
+    if (tc_) { tc_->drop_graph(); tc_->seen_key = TcState::GraphKey(); }
+    // every replica starts from rank 0's state, as dnn_trainer copies the master net to its devices (trainer.h:1206-1253)
+    if (loaded_) {
+        synchronize();
+        auto bcast = [&](DevBuf& b, size_t bytes) {
+            if (b.p && bytes) nccl_->check(nccl_->Broadcast(b.p, b.p, bytes, /*ncclUint8*/ 1, 0, comm_, comm_stream_), "ncclBroadcast");
+        };
+        const size_t np = plan_.num_params;
+        bcast(params_, np * 4);
+        bcast(mom_, np * 4);
+        bcast(running_, running_.bytes);
+        bcast(nu_dev_, sizeof(unsigned long long) * num_updates_.size());
+        if (adam_v_.p) { bcast(adam_v_, np * 4); bcast(adam_t_dev_, 4); }
+        AB_CUDA(cudaStreamSynchronize(comm_stream_));
+        if (tc_) tc_->fwd_packs_valid = false;
+    }
 }
 
 // sum-all-reduce of grads[lo, hi) on the communication stream, ordered after everything enqueued so far
@@ -249,11 +242,10 @@ void Engine::comm_init(const void* id128, int rank, int world)
 void Engine::allreduce_range(size_t lo, size_t hi)
 {
     if (world_ <= 1 || hi <= lo) return;
-    static thread_local int slot = 0;
-    cudaEvent_t ev = ev_bucket_[slot++ % 8];
+    cudaEvent_t ev = ev_bucket_[bucket_slot_++ % 8];
     AB_CUDA(cudaEventRecord(ev, stream_));
     AB_CUDA(cudaStreamWaitEvent(comm_stream_, ev, 0));
-    float* g = grads_.as<float>() + lo;
+    float* g = grads_.as<float>() + lo;   // (hi may be num_params + 1: the loss slot rides with the topmost bucket)
     nccl_->check(nccl_->AllReduce(g, g, hi - lo, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm_, comm_stream_), "ncclAllReduce");
 }
 

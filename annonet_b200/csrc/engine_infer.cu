@@ -1,8 +1,10 @@
 // Inference side of the engine: RuntimeNet::Forward / Process (NetPimpl.cpp:287-298) and the tiled
 // annonet_infer() (annonet_infer.cpp:32-185) with image, blend canvas and label map resident in HBM.
 #include "engine.h"
+#include "nccl_api.h"
 #include "tiling.h"
 
+#include <cmath>
 #include <cstring>
 
 namespace ab {
@@ -107,19 +109,78 @@ void Engine::process_host(const uint8_t* img_host, int h, int w, const double* g
     synchronize();
 }
 
-void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, int rank, int world)
+namespace {
+
+// One rank's share of a sharded annonet_infer(): a contiguous band of tile ROWS.
+struct Band {
+    int t0 = 0, t1 = 0;        // tiles [t0, t1)
+    int own0 = 0, own1 = -1;   // image rows this rank owns (union of its tiles' non-overlapping rectangles): it runs their argmax
+    int f0 = 0, f1 = -1;       // image rows its tiles touch (union of the full rectangles): the extent of its private canvas
+    bool empty() const { return t1 <= t0; }
+};
+
+// Tiles arrive row by row (tiling.cpp:57-83).  Rows are dealt to the ranks as contiguous bands of near-equal COST (the
+// pixels the net actually runs: every tile is enlarged to 64k + 63) -- not round-robin: neighbouring rows share a seam, so
+// a band exchanges at most two seams, and 19 rows over 8 ranks cost max 3 rows either way but far less traffic.
+std::vector<Band> plan_bands(const std::vector<Tile>& tiles, int world, int levels)
+{
+    std::vector<int> row_start;   // first tile of each tile row
+    std::vector<double> row_cost;
+    for (size_t i = 0; i < tiles.size(); ++i) {
+        if (i == 0 || tiles[i].full[1] != tiles[i - 1].full[1]) { row_start.push_back((int)i); row_cost.push_back(0); }
+        const int fw = tiles[i].full[2] - tiles[i].full[0] + 1, fh = tiles[i].full[3] - tiles[i].full[1] + 1;
+        row_cost.back() += (double)recommended_input_dimension(fw, levels) * recommended_input_dimension(fh, levels);
+    }
+    const int rows = (int)row_start.size();
+    row_start.push_back((int)tiles.size());
+    double total = 0;
+    for (double c : row_cost) total += c;
+    std::vector<Band> bands(world);
+    int j = 0;
+    double done = 0;
+    for (int r = 0; r < world; ++r) {
+        const int ja = j;
+        const double target = total * (r + 1) / world;
+        // take rows while that brings the running cost closer to this rank's share of the total; leave enough rows for the rest
+        while (j < rows && (rows - j > world - 1 - r) && (j == ja ? true : std::abs(done + row_cost[j] - target) <= std::abs(done - target))) done += row_cost[j++];
+        if (r == world - 1) while (j < rows) done += row_cost[j++];
+        if (j == ja && j < rows && rows - j >= world - r) done += row_cost[j++];
+        Band& b = bands[r];
+        b.t0 = row_start[ja]; b.t1 = row_start[j];
+        if (b.empty()) continue;
+        b.own0 = tiles[b.t0].non_overlapping[1]; b.own1 = tiles[b.t1 - 1].non_overlapping[3];
+        b.f0 = tiles[b.t0].full[1]; b.f1 = tiles[b.t1 - 1].full[3];
+    }
+    return bands;
+}
+
+}  // namespace
+
+// annonet_infer() (annonet_infer.cpp:32-185).  One process per GPU: after ab_comm_init every rank calls this with the same
+// image; rank r runs the tiles of band r into a PRIVATE canvas that spans only the rows its tiles touch, the ranks exchange
+// the seam strips with their two neighbours (each <= 63 overlap rows x K planes; ncclSend/Recv), every rank runs the argmax of the
+// rows it owns and the label strips (2 bytes per pixel) are broadcast so that every rank holds the whole label map.
+// No all-reduce, no full-size canvas per rank.  world = 1 is the same code with one band.
+void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
+                                uint16_t* labels_dev)
 {
     if (!loaded_) throw state_error("no net loaded");
     AB_CUDA(cudaSetDevice(device_));
     const int K = plan_.class_count;
     const int ov = (1 << (plan_.levels + 1)) - 1;  // TrainingNet::GetRequiredInputDimension, annonet_infer_main.cpp:421-427
     const std::vector<Tile> tiles = get_tiles(w, h, max_tile_w, max_tile_h, ov, ov);
-    canvas_.reserve((size_t)K * h * w * sizeof(float));
-    AB_CUDA(cudaMemsetAsync(canvas_.p, 0, (size_t)K * h * w * sizeof(float), stream_));
-    int row = -1, last_top = INT32_MIN;
-    for (const Tile& t : tiles) {
-        if (t.full[1] != last_top) { ++row; last_top = t.full[1]; }
-        if (world > 1 && row % world != rank) continue;
+    const std::vector<Band> bands = plan_bands(tiles, world_, plan_.levels);
+    const Band& me = bands[rank_];
+    const long long W = w;
+    const int rows = me.empty() ? 0 : me.f1 - me.f0 + 1;
+    canvas_rows_ = rows; canvas_row0_ = me.empty() ? 0 : me.f0;
+    const size_t plane = (size_t)rows * W;
+    if (rows) {
+        canvas_.reserve((size_t)K * plane * sizeof(float));
+        AB_CUDA(cudaMemsetAsync(canvas_.p, 0, (size_t)K * plane * sizeof(float), stream_));
+    }
+    for (int ti = me.t0; ti < me.t1; ++ti) {
+        const Tile& t = tiles[ti];
         const int fw = t.full[2] - t.full[0] + 1, fh = t.full[3] - t.full[1] + 1;
         const int cx = t.full[0] + fw / 2, cy = t.full[1] + fh / 2;
         const int rw = recommended_input_dimension(fw, plan_.levels), rh = recommended_input_dimension(fh, plan_.levels);
@@ -132,20 +193,64 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
             k::extract_tile(img_dev, h, w, left, top, i_x_.as<float>(), rh, rw, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
             run_inference_graph(rh, rw);
         }
-        k::BlendArgs b;
+        k::BlendArgs b;   // canvas coordinates: image rows shifted by the band's first row
         b.logits = i_logits_.as<float>(); b.K = K; b.th = rh; b.tw = rw;
-        b.canvas = canvas_.as<float>(); b.H = h; b.W = w; b.left = left; b.top = top;
+        b.canvas = canvas_.as<float>(); b.H = rows; b.W = w; b.left = left; b.top = top - me.f0;
         for (int i = 0; i < 4; ++i) { b.full[i] = t.full[i]; b.unique[i] = t.unique[i]; }
+        b.full[1] -= me.f0; b.full[3] -= me.f0; b.unique[1] -= me.f0; b.unique[3] -= me.f0;
         k::blend_tile(b, stream_);
     }
-    AB_CUDA(cudaGetLastError());
-}
-
-void Engine::infer_finish_device(int h, int w, const double* gains, int ngains, uint16_t* labels_dev)
-{
-    const long long npix = (long long)h * w;
-    const double* gd = upload_gains(gains_dev_, gains, ngains, plan_.class_count, stream_);
-    k::argmax_labels(canvas_.as<float>(), npix, plan_.class_count, npix, gd, labels_dev, stream_);
+    // ---- seams: what my tiles added to rows a neighbour owns goes there, what the neighbours' tiles added to my rows comes here
+    if (world_ > 1) {
+        int prev = -1, next = -1;
+        for (int r = rank_ - 1; r >= 0 && prev < 0; --r) if (!bands[r].empty()) prev = r;
+        for (int r = rank_ + 1; r < world_ && next < 0; ++r) if (!bands[r].empty()) next = r;
+        struct Strip { int peer, y0, y1; };   // image rows [y0, y1]
+        std::vector<Strip> out, in;
+        if (!me.empty()) {
+            if (prev >= 0 && me.f0 < me.own0) out.push_back({prev, me.f0, me.own0 - 1});
+            if (next >= 0 && me.f1 > me.own1) out.push_back({next, me.own1 + 1, me.f1});
+            if (prev >= 0 && bands[prev].f1 >= me.own0) in.push_back({prev, me.own0, bands[prev].f1});
+            if (next >= 0 && bands[next].f0 <= me.own1) in.push_back({next, bands[next].f0, me.own1});
+        }
+        size_t in_floats = 0;
+        for (const Strip& s : in) in_floats += (size_t)K * (s.y1 - s.y0 + 1) * W;
+        seam_.reserve(std::max<size_t>(in_floats, 1) * sizeof(float));
+        AB_CUDA(cudaStreamSynchronize(stream_));   // (first use: NCCL sets up its connections on its own streams)
+        nccl_->check(nccl_->GroupStart(), "ncclGroupStart");
+        for (const Strip& s : out)
+            for (int k = 0; k < K; ++k)
+                nccl_->check(nccl_->Send(canvas_.as<float>() + k * plane + (size_t)(s.y0 - me.f0) * W, (size_t)(s.y1 - s.y0 + 1) * W, /*ncclFloat32*/ 7,
+                                         s.peer, comm_, stream_), "ncclSend");
+        size_t off = 0;
+        for (const Strip& s : in) {
+            nccl_->check(nccl_->Recv(seam_.as<float>() + off, (size_t)K * (s.y1 - s.y0 + 1) * W, 7, s.peer, comm_, stream_), "ncclRecv");
+            off += (size_t)K * (s.y1 - s.y0 + 1) * W;
+        }
+        nccl_->check(nccl_->GroupEnd(), "ncclGroupEnd");
+        off = 0;
+        for (const Strip& s : in) {
+            const size_t n = (size_t)(s.y1 - s.y0 + 1) * W;
+            for (int k = 0; k < K; ++k)
+                k::add_inplace(canvas_.as<float>() + k * plane + (size_t)(s.y0 - me.f0) * W, seam_.as<float>() + off + k * n, (long long)n, stream_);
+            off += (size_t)K * n;
+        }
+    }
+    // ---- argmax of the rows I own, straight into the caller's label map; then every rank broadcasts its strip
+    const double* gd = upload_gains(gains_dev_, gains, ngains, K, stream_);
+    if (!me.empty()) {
+        const long long n = (long long)(me.own1 - me.own0 + 1) * W;
+        k::argmax_labels(canvas_.as<float>() + (size_t)(me.own0 - me.f0) * W, (long long)plane, K, n, gd, labels_dev + (size_t)me.own0 * W, stream_);
+    }
+    if (world_ > 1) {
+        nccl_->check(nccl_->GroupStart(), "ncclGroupStart");
+        for (int r = 0; r < world_; ++r) {
+            if (bands[r].empty()) continue;
+            uint16_t* p = labels_dev + (size_t)bands[r].own0 * W;
+            nccl_->check(nccl_->Broadcast(p, p, (size_t)(bands[r].own1 - bands[r].own0 + 1) * W * 2, /*ncclUint8*/ 1, r, comm_, stream_), "ncclBroadcast");
+        }
+        nccl_->check(nccl_->GroupEnd(), "ncclGroupEnd");
+    }
     AB_CUDA(cudaGetLastError());
 }
 
@@ -157,12 +262,16 @@ void Engine::infer_tiled_host(const uint8_t* img_host, int h, int w, int max_til
     i_img_.reserve(bytes);
     // large images: copy straight from the caller's memory (the driver stages pageable memory itself)
     AB_CUDA(cudaMemcpyAsync(i_img_.p, img_host, bytes, cudaMemcpyHostToDevice, stream_));
-    infer_tiled_device(i_img_.as<uint8_t>(), h, w, max_tile_w, max_tile_h, 0, 1);
     i_labels_.reserve((size_t)h * w * 2);
-    infer_finish_device(h, w, gains, ngains, i_labels_.as<uint16_t>());
+    infer_tiled_device(i_img_.as<uint8_t>(), h, w, max_tile_w, max_tile_h, gains, ngains, i_labels_.as<uint16_t>());
     AB_CUDA(cudaMemcpyAsync(labels_host, i_labels_.p, (size_t)h * w * 2, cudaMemcpyDeviceToHost, stream_));
-    if (blended_host)
-        AB_CUDA(cudaMemcpyAsync(blended_host, canvas_.p, (size_t)plan_.class_count * h * w * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+    if (blended_host) {   // the blended logits of the rows this rank's canvas holds (one process: the whole image), other rows zero
+        const size_t hw = (size_t)h * w;
+        std::memset(blended_host, 0, (size_t)plan_.class_count * hw * sizeof(float));
+        for (int k = 0; k < plan_.class_count && canvas_rows_; ++k)
+            AB_CUDA(cudaMemcpyAsync(blended_host + k * hw + (size_t)canvas_row0_ * w, canvas_.as<float>() + (size_t)k * canvas_rows_ * w,
+                                    (size_t)canvas_rows_ * w * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+    }
     synchronize();
 }
 

@@ -313,8 +313,8 @@ void Engine::level_values(int level, bool gradient, std::vector<float>& out, int
 // One step = ~390 kernels, many of them a few microseconds long (the coarse levels): launch-bound when issued one by
 // one.  The step is static (shapes, pointers, the bn counters live on the device), so it is captured once into a CUDA
 // graph and replayed while nothing it bakes in changes (TcState::GraphKey).  Not captured: the first step of a
-// configuration (lazy module loading, cudaFuncSetAttribute), per-kernel profiling, Adam (its step counter is a kernel
-// argument).  Data-parallel runs capture the step as segments split at the gradient-bucket boundaries and issue the NCCL
+// configuration (lazy module loading, cudaFuncSetAttribute) and per-kernel profiling (Adam's step counter lives on the
+// device, so Adam steps are captured like SGD steps).  Data-parallel runs capture the step as segments split at the gradient-bucket boundaries and issue the NCCL
 // all-reduces eagerly between them (TcState::graph_segs).
 void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update)
 {
@@ -322,7 +322,8 @@ void Engine::tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int 
     tc_ensure_train(n, h, w);
     TcState& T = *tc_;
     static const bool no_graph = getenv("AB_NO_GRAPH") != nullptr;
-    if (no_graph || k::prof_enabled() || hyper.solver != 0) { tc_train_body(imgs_dev, labels_dev, n, h, w, update, false); return; }
+    if (hyper.solver != 0 && update) ensure_adam_state();   // allocations must happen outside the capture
+    if (no_graph || k::prof_enabled()) { tc_train_body(imgs_dev, labels_dev, n, h, w, update, false); return; }
     TcState::GraphKey key;
     key.imgs = imgs_dev; key.labels = labels_dev; key.n = n; key.h = h; key.w = w; key.update = update; key.skip_dead = hyper.skip_dead_layers;
     key.world = world_; key.solver = hyper.solver; key.loss_scale = hyper.loss_scale;
@@ -452,7 +453,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             k::fill_zero(T.tg.level[l].p, (size_t)T.tg.geo[l].positions() * plan_.level_channels[l] * sizeof(h16), stream_);
     const size_t np = plan_.num_params;
     k::fill_zero(G, np * sizeof(float), stream_);
-    const int nbuckets = 4;
+    static const int nbuckets = getenv("AB_BUCKETS") ? std::max(1, atoi(getenv("AB_BUCKETS"))) : 2;
     // eager: all-reduce the bucket now;  capturing: the bucket ends a graph segment (tc_train_step issues the all-reduce at replay)
     auto bucket_ready = [&](size_t lo, size_t hi) {
         if (!capture) { allreduce_range(lo, hi); return; }
@@ -462,6 +463,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         AB_CUDA(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
     };
     size_t bucket_hi = np;
+    if (world_ > 1) { k::loss_to_slot(t_loss_.as<double>(), G + np, stream_); bucket_hi = np + 1; }   // the loss rides with the first bucket
     for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
         const ConvGroup& g = plan_.groups[gi];
         TcGroup& t = T.groups[gi];
@@ -510,6 +512,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
             AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
         }
+        k::slot_to_loss(G + np, t_loss_.as<double>(), world_, stream_);   // mean of the ranks' losses (trainer.h:1206-1253)
     }
     if (update) optimizer_step();
     AB_CUDA(cudaMemcpyAsync(loss_host_, t_loss_.p, sizeof(double), cudaMemcpyDeviceToHost, stream_));

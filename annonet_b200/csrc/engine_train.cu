@@ -127,6 +127,7 @@ void Engine::backward_train(int n, int h, int w)
     const size_t np = plan_.num_params;
     const int nbuckets = 4;
     size_t bucket_hi = np;
+    if (world_ > 1) { loss_to_slot(t_loss_.as<double>(), grads_.as<float>() + np, stream_); bucket_hi = np + 1; }
 
     for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
         const ConvGroup& g = plan_.groups[gi];
@@ -194,7 +195,22 @@ void Engine::backward_train(int n, int h, int w)
         allreduce_range(0, bucket_hi);
         AB_CUDA(cudaEventRecord(ev_comm_done_, comm_stream_));
         AB_CUDA(cudaStreamWaitEvent(stream_, ev_comm_done_, 0));
+        slot_to_loss(grads_.as<float>() + np, t_loss_.as<double>(), world_, stream_);   // mean of the ranks' losses
     }
+}
+
+// adam's second-moment arena and its device-side step counter; allocated outside any stream capture (tc_train_step calls this
+// before it starts capturing)
+void Engine::ensure_adam_state()
+{
+    if (adam_v_.p) return;
+    const size_t np = plan_.num_params;
+    adam_v_.reserve(np * 4);
+    adam_t_dev_.reserve(256);
+    AB_CUDA(cudaMemsetAsync(adam_v_.p, 0, np * 4, stream_));
+    const float t0 = (float)adam_t_;
+    AB_CUDA(cudaMemcpyAsync(adam_t_dev_.p, &t0, 4, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaStreamSynchronize(stream_));
 }
 
 void Engine::optimizer_step()
@@ -205,10 +221,10 @@ void Engine::optimizer_step()
         sgd_step(params_.as<float>(), grads_.as<float>(), mom_.as<float>(), lr_mul_.as<float>(), wd_mul_.as<float>(), np,
                  (float)hyper.learning_rate, (float)hyper.weight_decay, (float)hyper.momentum, gscale, stream_);
     } else {
-        if (!adam_v_.p) { adam_v_.reserve(np * 4); AB_CUDA(cudaMemsetAsync(adam_v_.p, 0, np * 4, stream_)); }
+        ensure_adam_state();
         ++adam_t_;
         adam_step(params_.as<float>(), grads_.as<float>(), mom_.as<float>(), adam_v_.as<float>(), lr_mul_.as<float>(), wd_mul_.as<float>(),
-                  np, (float)adam_t_, (float)hyper.learning_rate, (float)hyper.weight_decay, (float)hyper.adam_beta1,
+                  np, adam_t_dev_.as<float>(), (float)hyper.learning_rate, (float)hyper.weight_decay, (float)hyper.adam_beta1,
                   (float)hyper.adam_beta2, gscale, stream_);
     }
 }

@@ -105,14 +105,21 @@ struct BlendArgs {
     int full[4], unique[4];                     // inclusive l,t,r,b
 };
 void blend_tile(const BlendArgs& a, cudaStream_t st);
+// dst += src (a neighbour rank's seam strip into the blend canvas)
+void add_inplace(float* dst, const float* src, long long n, cudaStream_t st);
 
 // ---- optimizer --------------------------------------------------------------------------------
 // sgd::operator() (solvers.h:155-185): v = m*v - (wd*wdm)*(lr*lrm)*w - (lr*lrm)*g ; w += v
 void sgd_step(float* w, const float* g, float* v, const float* lr_mul, const float* wd_mul, long long n,
               float lr, float wd, float momentum, float grad_scale, cudaStream_t st);
 // adam (solvers.h:353-372, cpu_dlib.cpp:704-743)
+// t_dev: device-side step counter, advanced by the launch itself (the step stays a static CUDA graph)
 void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul, const float* wd_mul, long long n,
-               float t, float lr, float wd, float beta1, float beta2, float grad_scale, cudaStream_t st);
+               float* t_dev, float lr, float wd, float beta1, float beta2, float grad_scale, cudaStream_t st);
+// data parallel: the step loss rides in one extra float behind the gradient arena through the last all-reduce
+// (dnn_trainer reports the mean of the device losses, trainer.h:1206-1253)
+void loss_to_slot(const double* loss, float* slot, cudaStream_t st);
+void slot_to_loss(const float* slot, double* loss, int world, cudaStream_t st);
 void fill_zero(void* p, size_t bytes, cudaStream_t st);
 
 }  // namespace k

@@ -131,13 +131,20 @@ __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ w, const f
     w[i] = w[i] + nv;
 }
 
+__global__ void bump_kernel(float* t) { *t += 1.f; }
+__global__ void loss_to_slot_kernel(const double* loss, float* slot) { *slot = (float)*loss; }
+__global__ void slot_to_loss_kernel(const float* slot, double* loss, float inv_world) { *loss = (double)(*slot * inv_world); }
+
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, const float* __restrict__ lr_mul, const float* __restrict__ wd_mul,
-                                                   const long long n, const float alpha_base, const float lr, const float wd,
+                                                   const long long n, const float* __restrict__ t_dev, const float lr, const float wd,
                                                    const float b1, const float b2, const float grad_scale)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    // bias correction from the device-side step counter (a kernel argument would pin the step into a captured CUDA graph)
+    const float t = *t_dev;
+    const float alpha_base = sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
     const float lri = (float)((double)lr * (double)lr_mul[i]);
     const float wdi = (float)((double)wd * (double)wd_mul[i]);
     const float alpha = lri * alpha_base;
@@ -203,16 +210,41 @@ void sgd_step(float* w, const float* g, float* v, const float* lr_mul, const flo
     count_launch();
 }
 
-void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul, const float* wd_mul, long long n, float t, float lr,
+void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul, const float* wd_mul, long long n,
+               float* t_dev, float lr,
                float wd, float beta1, float beta2, float grad_scale, cudaStream_t st)
 {
     ProfScope ps(F_OPTIMIZER, 0, 36.0 * n, st);
-    const float alpha_base = std::sqrt(1 - std::pow(beta2, t)) / (1 - std::pow(beta1, t));
-    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, m, v, lr_mul, wd_mul, n, alpha_base, lr, wd, beta1, beta2, grad_scale);
-    count_launch();
+    bump_kernel<<<1, 1, 0, st>>>(t_dev);   // t = t + 1 (solvers.h:262: the first step runs with t = 1)
+    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, g, m, v, lr_mul, wd_mul, n, t_dev, lr, wd, beta1, beta2, grad_scale);
+    count_launch(2);
 }
 
 void fill_zero(void* p, size_t bytes, cudaStream_t st) { cudaMemsetAsync(p, 0, bytes, st); }
+
+__global__ void __launch_bounds__(256) add_inplace_kernel(float* __restrict__ dst, const float* __restrict__ src, long long n)
+{
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += (long long)gridDim.x * blockDim.x * 4) {
+        if (i + 3 < n && ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0)) {
+            float4 a = *reinterpret_cast<float4*>(dst + i);
+            const float4 b = *reinterpret_cast<const float4*>(src + i);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+            *reinterpret_cast<float4*>(dst + i) = a;
+        } else
+            for (long long j = i; j < n && j < i + 4; ++j) dst[j] += src[j];
+    }
+}
+
+void add_inplace(float* dst, const float* src, long long n, cudaStream_t st)
+{
+    if (n <= 0) return;
+    ProfScope ps(F_BLEND, 0, 12.0 * n, st);
+    add_inplace_kernel<<<(unsigned)std::min<long long>((n / 4 + 255) / 256 + 1, 148 * 16), 256, 0, st>>>(dst, src, n);
+    count_launch();
+}
+
+void loss_to_slot(const double* loss, float* slot, cudaStream_t st) { loss_to_slot_kernel<<<1, 1, 0, st>>>(loss, slot); count_launch(); }
+void slot_to_loss(const float* slot, double* loss, int world, cudaStream_t st) { slot_to_loss_kernel<<<1, 1, 0, st>>>(slot, loss, 1.f / world); count_launch(); }
 
 }  // namespace k
 }  // namespace ab

@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 CROP, BATCH, CLASSES = 255, 32, 3
 INFER_SIZE, INFER_TILE = 1024, 1024
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "annonet_ref")
-FWD_FLOP_PER_PX = 170281.0  # live layers, SURVEY §8d
+FWD_FLOP_PER_PX = 85140.0  # live layers: SURVEY App. B sums to 42,570 MAC per input pixel (the survey's 170,281 double-counted)
 
 
 def peaks():
@@ -202,7 +202,7 @@ def own_arm(args):
     clocks = ClockSampler(local).start()   # long before the timed region (nvidia-smi start-up)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    precision = ab.AB_PRECISION_F16 if args.precision == "bf16" else ab.AB_PRECISION_FP32
+    precision = ab.AB_PRECISION_F16 if args.precision == "f16" else ab.AB_PRECISION_FP32
 
     net = ab.TrainingNet(local, precision)
     net.Initialize(CLASSES, 1.0, 1, seed=1)         # identical weights on every rank (same seed)
@@ -316,9 +316,9 @@ def own_arm(args):
     # averaged per launch like `achieved` (profiles/r01_traffic.json, written from the committed ncu csv by profiles/traffic_from_ncu.py)
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_traffic.json")) as f:
             tj = json.load(f)
-        ent = tj.get("bf16" if precision != ab.AB_PRECISION_FP32 else "fp32", {}).get(top["name"])
+        ent = tj.get("f16" if precision != ab.AB_PRECISION_FP32 else "fp32", {}).get(top["name"])
         if ent:
             traffic, traffic_src = ent["dram_bytes_per_launch"], tj.get("source")
     except (OSError, ValueError, KeyError):
@@ -344,7 +344,7 @@ def own_arm(args):
     line = {
         "metric": "train_crops_per_s", "value": crops / (ms * 1e-3), "unit": "crops/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32" if precision == ab.AB_PRECISION_FP32 else "bf16", "data": "synthetic",
+        "dtype": "f32" if precision == ab.AB_PRECISION_FP32 else "f16", "data": "synthetic",
         "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP} per GPU, {CLASSES} classes, weighted per-pixel loss, SGD (BASELINE configs[1])",
                    "net": "net_type LEVEL_COUNT=6 full width, 2,279,571 params, random init", "parallelism": f"dp{world}",
                    "l2": "no flush: each step streams GBs of activations, far beyond the 126 MB L2",
@@ -396,26 +396,27 @@ def bench_infer(ab, train_net, device, precision, torch, reps=3):
 
 
 def bench_infer_sharded(ab, device, precision, torch, dist, rank, world, size=16384, tile=1024, classes=8, reps=2):
-    """BASELINE configs[2]: annonet_infer() of one size x size image, 8 classes; rank r runs the tile rows r, r + world, ...
-    into its private blend canvas, ONE all-reduce sums the canvases, every rank runs the argmax.
-    Device-resident image and label map; CUDA events on the engine's stream, max over ranks."""
-    import numpy as np
+    """BASELINE configs[2]: annonet_infer() of one size x size image, 8 classes.  Every rank makes the same ab_infer_tiled_device
+    call; the engine deals the tile rows to the ranks as contiguous bands of equal cost, exchanges the seam strips between
+    neighbours (ncclSend/Recv) and broadcasts the 2-byte label strips (DESIGN.md §5).  Device-resident image and label map;
+    CUDA events on the engine's stream, max over ranks."""
     net = ab.TrainingNet(device, precision)
     net.Initialize(classes, 1.0, 1, seed=2)
     rt = net.GetRuntimeNet(device, precision)
     del net
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(ab.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        rt.comm_init(bytes(uid.cpu().numpy().tobytes()), rank, world)
     g = torch.Generator(device="cuda").manual_seed(7)
     d_img = torch.randint(0, 256, (size, size, 3), dtype=torch.uint8, device="cuda", generator=g)
     d_lab = torch.empty((size, size), dtype=torch.int16, device="cuda")
     stream = torch.cuda.ExternalStream(rt.stream(), device=device)
 
     def once():
-        ptr, n = rt.infer_partial_device(d_img.data_ptr(), size, size, tile, tile, rank, world)
-        if world > 1:
-            with torch.cuda.stream(stream):
-                canvas = _as_tensor(torch, ptr, n, device)
-                dist.all_reduce(canvas)
-        rt.infer_finish_device(size, size, d_lab.data_ptr())
+        rt.infer_device(d_img.data_ptr(), size, size, tile, tile, d_lab.data_ptr())
 
     once()
     rt.synchronize()
@@ -433,15 +434,9 @@ def bench_infer_sharded(ab, device, precision, torch, dist, rank, world, size=16
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t[0])
-    return {"workload": f"annonet_infer of one {size}x{size} RGB image, {classes} classes, tile {tile} (19 x 19 tiles), tile rows sharded over {world} GPU(s), "
-                        "one NCCL all-reduce of the blend canvas", "mpix_per_s": size * size / (ms * 1e-3) / 1e6, "ms": ms, "n_gpus": world}
-
-
-def _as_tensor(torch, ptr, n, device):
-    """a torch view of engine-owned device memory (the blend canvas) for torch.distributed's NCCL all-reduce"""
-    class _Cai:
-        __cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 3, "strides": None}
-    return torch.as_tensor(_Cai(), device=torch.device("cuda", device))
+    return {"workload": f"annonet_infer of one {size}x{size} RGB image, {classes} classes, tile {tile} (19 x 19 tiles), tile rows sharded over {world} GPU(s) "
+                        "as contiguous bands, seam strips exchanged between neighbours, label strips broadcast",
+            "mpix_per_s": size * size / (ms * 1e-3) / 1e6, "ms": ms, "n_gpus": world}
 
 
 def main():
@@ -450,8 +445,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("AB_PRECISION", "bf16"), choices=["fp32", "bf16"],
-                    help="bf16: tcgen05 tensor-core path (fp32 accumulate, fp32 master weights); fp32: FMA parity path")
+    ap.add_argument("--precision", default=os.environ.get("AB_PRECISION", "f16"), choices=["fp32", "f16"],
+                    help="f16: tcgen05 tensor-core path (fp16 operands, split hi + lo training forward, fp32 accumulate, fp32 master weights); "
+                         "fp32: FMA parity path")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-infer", action="store_true", help="skip the secondary inference measurement")
     ap.add_argument("--no-infer16k", action="store_true", help="skip the sharded 16384^2 tiled inference (BASELINE configs[2])")

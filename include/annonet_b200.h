@@ -127,22 +127,19 @@ ab_status ab_process(ab_net* net, const uint8_t* image_hwc, int h, int w, const 
 ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, int overlap_x, int overlap_y,
                        ab_tile* out, int cap, int* count);
 
-/* annonet_infer() (annonet_infer.cpp:32-185, without the detection-level blob filter): tiles ->
+/* annonet_infer() (annonet_infer.cpp:32-185; the detection-level blob filter is ab_filter_detections): tiles ->
  * enlarge to 64w+63 -> clamp-to-edge fill -> forward -> blend -> argmax(+gain), all on the device.
- * rank/world shard the tile list (tile i belongs to rank i % world); with world > 1 each caller
- * receives labels only where its own tiles' unique rectangles... see ab_infer_tiled_merge.
- * labels_host: h*w uint16.  blended_host (optional): class_count*h*w f32 (temp.blended_output). */
+ * labels_host: h*w uint16.  blended_host (optional): class_count*h*w f32 (temp.blended_output).
+ * Multi-GPU: after ab_comm_init(net, id, rank, world) every rank makes the SAME call; the tile rows are dealt to
+ * the ranks as contiguous bands of equal cost, each rank blends its band into a private canvas spanning only the rows its
+ * tiles touch, neighbouring ranks exchange the seam strips (ncclSend/Recv), each rank runs the argmax of the rows it owns
+ * and the 2-byte label strips are broadcast: every rank returns the whole label map.  (blended_host then holds this
+ * rank's rows only, zero elsewhere.) */
 ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, int max_tile_w, int max_tile_h,
                          const double* gains, int ngains, uint16_t* labels_host, float* blended_host);
 /* Same with image and labels resident in device memory (image_dev: h*w*3 u8, labels_dev: h*w u16). */
 ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,
                                 const double* gains, int ngains, void* labels_dev);
-/* Multi-GPU inference: this rank runs the tiles of rows  row % world == rank  of the
- * tile grid into its private blend canvas; canvases are summed by the caller's collective
- * (NCCL all-reduce on the pointer returned here) before ab_infer_finish runs the argmax. */
-ab_status ab_infer_tiled_partial(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,
-                                 int rank, int world, void** canvas_dev, size_t* canvas_floats);
-ab_status ab_infer_finish(ab_net* net, int h, int w, const double* gains, int ngains, void* labels_dev);
 
 /* ---- training ----------------------------------------------------------------------------- */
 ab_status ab_set_hyper(ab_net* net, int id, double value);

@@ -454,6 +454,35 @@ def sgd_step(net: Net, grads: Dict[int, np.ndarray], momentum_state: Dict[int, n
         l["params"] = p.reshape(l["params"].shape)
 
 
+def adam_step(net: Net, grads: Dict[int, np.ndarray], state: Dict[int, Dict[str, np.ndarray]], lr: float,
+              weight_decay: float = 0.001, momentum1: float = 0.9, momentum2: float = 0.999) -> None:
+    """adam::operator() + update_considering_bias, dlib/dlib/dnn/solvers.h:225-372, with cpu::compute_adam_update,
+    dlib/dlib/cuda/cpu_dlib.cpp:704-743 (fp32 arithmetic, eps = 1e-8, bias-corrected step size
+    alpha = lr * sqrt(1 - b2^t) / (1 - b1^t)) and add_layer::update_parameters, core.h:1011-1023.  In place on net and state."""
+    for i, l in net.param_layers():
+        if l["type"] == "affine":
+            continue
+        p = l["params"].reshape(-1)
+        gr = grads[i].reshape(-1).astype(F32)
+        st = state.setdefault(i, {"m": np.zeros_like(p), "v": np.zeros_like(p), "t": 0})
+        st["t"] += 1
+        t = F32(st["t"])
+        lrm, wdm, blrm, bwdm = l["multipliers"]
+        bias_off = p.size - l["num_filters"] if l["type"] in ("con", "cont") else p.size // 2
+        lr_w = F32(float(F32(lr)) * lrm)
+        wd_w = F32(float(F32(weight_decay)) * wdm)
+        b1, b2 = F32(momentum1), F32(momentum2)
+        s = np.empty_like(p)
+        for lo, hi, lr_, wd_ in ((0, bias_off, lr_w, wd_w), (bias_off, p.size, F32(lr_w * F32(blrm)), F32(wd_w * F32(bwdm)))):
+            alpha = F32(lr_ * F32(np.sqrt(F32(1) - F32(np.power(b2, t)))) / (F32(1) - F32(np.power(b1, t))))
+            g = (wd_ * p[lo:hi] + gr[lo:hi]).astype(F32)
+            st["m"][lo:hi] = b1 * st["m"][lo:hi] + (F32(1) - b1) * g
+            st["v"][lo:hi] = b2 * st["v"][lo:hi] + (F32(1) - b2) * g * g
+            s[lo:hi] = -alpha * st["m"][lo:hi] / (np.sqrt(st["v"][lo:hi]) + F32(1e-8))
+        p += s
+        l["params"] = p.reshape(l["params"].shape)
+
+
 def to_label(logits_khw: np.ndarray, gains: Sequence[float] = ()) -> np.ndarray:
     """loss_multiclass_log_per_pixel_::to_label, loss.h:2921-2969 / annonet_infer.cpp:170-185:
     argmax_k float(logit_k + gain_k), strict '>' from -inf: lowest index wins ties, all-NaN -> 65535."""

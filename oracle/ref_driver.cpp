@@ -113,7 +113,7 @@ void synthetic_image(NetPimpl::input_type& img, long h, long w, unsigned seed)
 
 int usage()
 {
-    std::cerr << "usage: annonet_ref <config|materialize|runtime|forward|forward_layers|process|infer|grads|train|set_weights|tiles|recommended|bench_infer|bench_train> ...\n";
+    std::cerr << "usage: annonet_ref <config|materialize|runtime|forward|forward_layers|process|infer|grads|train|adam|set_weights|tiles|recommended|bench_infer|bench_train> ...\n";
     return 2;
 }
 
@@ -199,7 +199,8 @@ int main(int argc, char** argv) try
         return ref_grads(arg(2), load_images(arg(3), n, h, w), load_labels(arg(4), arg(5), n, h, w), arg(9), argc > 10);
     }
     if (cmd == "train") {
-        // <net> <imgs> <labels.u16> <weights.f32> <N> <H> <W> <lr> <steps> <out_net> [bn_window] [out_anet]
+        // <net> <imgs> <labels.u16> <weights.f32> <N> <H> <W> <lr> <steps> <out_net> [bn_window] [out_anet] [sync_file]
+        // sync_file: TrainingNet::SetSynchronizationFile(name, 0 s) -- dnn_trainer writes its v13 state file (trainer.h:931-964)
         // The files hold steps*N samples; step s consumes samples [s*N, (s+1)*N).
         const long n = std::stol(arg(6)), h = std::stol(arg(7)), w = std::stol(arg(8));
         const double lr = std::stod(arg(9));
@@ -213,6 +214,7 @@ int main(int argc, char** argv) try
         t.SetLearningRateShrinkFactor(1.0);  // no plateau logic inside a parity run
         if (argc > 12 && std::string(arg(12)) != "-")
             t.SetAllBatchNormalizationRunningStatsWindowSizes(std::stoul(arg(12)));
+        if (argc > 14) t.SetSynchronizationFile(arg(14), std::chrono::seconds(0));
         const auto t0 = std::chrono::steady_clock::now();
         for (long s = 0; s < steps; ++s) {
             std::vector<NetPimpl::input_type> bi(imgs.begin() + s * n, imgs.begin() + (s + 1) * n);
@@ -225,6 +227,26 @@ int main(int argc, char** argv) try
         if (argc > 13) rt.Serialize(arg(13));
         std::cout << "{\"seconds\": " << secs << ", \"crops_per_s\": " << (n * steps / secs) << ", \"threads\": " << host_threads()
                   << ", \"learning_rate\": " << t.GetLearningRate() << "}" << std::endl;
+        return 0;
+    }
+    if (cmd == "adam") {
+        // <n> <steps> <lr> <wd> <beta1> <beta2> <params.f32> <grads.f32 (steps*n)> <out_params.f32>
+        // dlib's own Adam arithmetic (tt::compute_adam_update -> cpu::compute_adam_update, cpu_dlib.cpp:704-743) applied the
+        // way adam::operator() + add_layer::update_parameters do (solvers.h:225-260, core.h:1011-1023): t starts at 1.
+        const long n = std::stol(arg(2)), steps = std::stol(arg(3));
+        const float lr = std::stof(arg(4)), wd = std::stof(arg(5)), b1 = std::stof(arg(6)), b2 = std::stof(arg(7));
+        const auto pb = ref_io::slurp(arg(8)), gb = ref_io::slurp(arg(9));
+        if (static_cast<long>(pb.size()) != n * 4 || static_cast<long>(gb.size()) != n * steps * 4) throw std::runtime_error("adam: file size mismatch");
+        dlib::resizable_tensor params(n), grad(n), m(n), v(n), upd(n);
+        std::memcpy(params.host(), pb.data(), pb.size());
+        m = 0; v = 0;
+        for (long s = 0; s < steps; ++s) {
+            std::memcpy(grad.host(), gb.data() + s * n * 4, n * 4);
+            dlib::tt::compute_adam_update(0, n, upd, m, v, static_cast<float>(s + 1), lr, wd, b1, b2, params, grad);
+            dlib::tt::add(1, params, 1, upd);   // params += step (core.h:1019)
+        }
+        std::ofstream out(arg(10), std::ios::binary);
+        out.write(reinterpret_cast<const char*>(params.host()), n * 4);
         return 0;
     }
     if (cmd == "set_weights") {

@@ -125,6 +125,17 @@ def main():
             json.dump(dict(tiles=tiles, recommended=rec), f)
         print("loss", loss, out.strip())
 
+        # ---- dlib's own Adam arithmetic (tt::compute_adam_update) on a seeded vector: pins oracle adam_step
+        arng = np.random.default_rng(5)
+        n, steps = 1000, 4
+        params = arng.normal(0, 0.3, n).astype(np.float32)
+        grads = arng.normal(0, 1e-3, (steps, n)).astype(np.float32)
+        grads[:, :50] = 0   # exact zeros: m / (sqrt(v) + eps) with v = 0
+        lr, wd, b1, b2 = 0.01, 0.0005, 0.9, 0.999
+        params.tofile(p("adam_p.f32")); grads.tofile(p("adam_g.f32"))
+        run("adam", n, steps, repr(lr), repr(wd), repr(b1), repr(b2), p("adam_p.f32"), p("adam_g.f32"), p("adam_o.f32"))
+        np.savez(g("adam.npz"), params=params, grads=grads, out=np.fromfile(p("adam_o.f32"), np.float32), lr=lr, wd=wd, b1=b1, b2=b2)
+
 
 if __name__ == "__main__":
     main()

@@ -151,6 +151,45 @@ def test_two_training_steps_match_reference(ab):
     assert rel_err(mine_rt.Forward(g["image"]), ref_rt.Forward(g["image"])) < 5e-3
 
 
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+def test_adam_steps_match_the_oracle_solver(ab, precision):
+    """SetSolver("adam"): three steps of the engine's fused Adam kernel (device-side step counter, inside the CUDA graph on
+    the tensor-core path) against the oracle's restatement of dlib::adam (solvers.h:225-372, cpu_dlib.cpp:704-743), which
+    tests/test_oracle_golden.py pins to dlib's own compute_adam_update.  Each step: the engine's own gradient of the current
+    parameters feeds the oracle solver; the engine's parameters after the step must equal the oracle's."""
+    prec = ab.AB_PRECISION_FP32 if precision == "fp32" else ab.AB_PRECISION_F16
+    onet = df.random_net(class_count=3, seed=31) if precision == "f16" else df.parse_net(golden_bytes("net_small.dnn"))
+    data = df.serialize_net(onet)
+    rng = np.random.default_rng(41)
+    imgs = np.stack([synth_image(rng, 127, 127) for _ in range(2)])
+    labs = np.stack([synth_labels(rng, 127, 127, 3) for _ in range(2)])
+    wl = ab.pack_labels(labs, np.stack([ab.set_weights(l, 0.5, 0.5) for l in labs]))
+    net = ab.TrainingNet(0, prec)
+    net.Deserialize(data)
+    net.SetSolver("adam", 0.0005, 0.9, 0.999)
+    net.SetLearningRate(0.01)
+    probe = ab.TrainingNet(0, prec)
+    state = {}
+    for step in range(3):
+        probe.Deserialize(df.serialize_net(onet))
+        probe.compute_gradients(imgs, wl)
+        grads = {i: probe.layer_gradient(i) for i, _ in onet.param_layers()}
+        on.adam_step(onet, grads, state, 0.01, 0.0005, 0.9, 0.999)
+        net.StartTraining(imgs, wl)
+        net.sync()
+        mine = df.parse_net(net.Serialize())
+        for (i, a), (_, b) in zip(mine.param_layers(), onet.param_layers()):
+            # Adam's update is -alpha * m / (sqrt(v) + eps): where |g| ~ eps the quotient amplifies the last bits of g
+            assert np.max(np.abs(a["params"].reshape(-1) - b["params"].reshape(-1))) <= 2e-3 * 0.01 + 1e-6 * np.abs(b["params"]).max(), f"step {step} layer<{i}>"
+        # continue from the ENGINE's parameters so that rounding differences do not compound across steps
+        for (i, a), (_, b) in zip(mine.param_layers(), onet.param_layers()):
+            b["params"] = a["params"].copy()
+            if a["type"] == "bn":
+                for k in ("running_means", "running_variances", "num_updates", "means", "invstds"):
+                    if k in a:
+                        b[k] = a[k]
+
+
 def test_training_is_deterministic_and_loss_decreases(ab):
     losses = []
     for _ in range(2):

@@ -126,3 +126,20 @@ def test_tiles_match_reference_and_its_identities():
             assert on.recommended_input_dimension(int(m)) == d
     with pytest.raises(ValueError):
         on.recommended_input_dimension(32000)
+
+
+def test_adam_restatement_matches_dlib():
+    """oracle adam_step against dlib's own compute_adam_update (annonet_ref adam, tests/golden/adam.npz): 4 steps on a
+    parameter vector with a bias segment -- bit-exact up to the last fp32 bit of pow/sqrt"""
+    g = golden_npz("adam.npz")
+    n = g["params"].size
+    layer = {"type": "bn", "params": g["params"].copy().reshape(1, n, 1, 1), "multipliers": [1.0, 1.0, 1.0, 1.0]}
+
+    class FakeNet:
+        def param_layers(self):
+            return [(7, layer)]
+
+    state = {}
+    for s in range(g["grads"].shape[0]):
+        on.adam_step(FakeNet(), {7: g["grads"][s]}, state, float(g["lr"]), float(g["wd"]), float(g["b1"]), float(g["b2"]))
+    np.testing.assert_allclose(layer["params"].reshape(-1), g["out"], rtol=2e-6, atol=1e-9)
