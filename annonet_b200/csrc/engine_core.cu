@@ -136,7 +136,8 @@ void Engine::load(const NetModel& m)
             }
         }
     }
-    params_.reserve(np * 4); grads_.reserve((np + 1) * 4); mom_.reserve(np * 4);   // grads_[np]: the step loss of a data-parallel run lr_mul_.reserve(np * 4); wd_mul_.reserve(np * 4);
+    // grads_[np]: the step loss of a data-parallel run rides behind the gradients through the all-reduce
+    params_.reserve(np * 4); grads_.reserve((np + 1) * 4); mom_.reserve(np * 4); lr_mul_.reserve(np * 4); wd_mul_.reserve(np * 4);
     running_.reserve(std::max<size_t>(roff, 1) * 4);
     AB_CUDA(cudaMemcpy(params_.p, hp.data(), np * 4, cudaMemcpyHostToDevice));
     AB_CUDA(cudaMemcpy(lr_mul_.p, lrm.data(), np * 4, cudaMemcpyHostToDevice));

@@ -223,9 +223,11 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
                 nccl_->check(nccl_->Send(canvas_.as<float>() + k * plane + (size_t)(s.y0 - me.f0) * W, (size_t)(s.y1 - s.y0 + 1) * W, /*ncclFloat32*/ 7,
                                          s.peer, comm_, stream_), "ncclSend");
         size_t off = 0;
-        for (const Strip& s : in) {
-            nccl_->check(nccl_->Recv(seam_.as<float>() + off, (size_t)K * (s.y1 - s.y0 + 1) * W, 7, s.peer, comm_, stream_), "ncclRecv");
-            off += (size_t)K * (s.y1 - s.y0 + 1) * W;
+        for (const Strip& s : in) {   // one receive per plane: sends and receives pair up one to one, in order
+            const size_t n = (size_t)(s.y1 - s.y0 + 1) * W;
+            for (int k = 0; k < K; ++k)
+                nccl_->check(nccl_->Recv(seam_.as<float>() + off + k * n, n, 7, s.peer, comm_, stream_), "ncclRecv");
+            off += (size_t)K * n;
         }
         nccl_->check(nccl_->GroupEnd(), "ncclGroupEnd");
         off = 0;
