@@ -57,7 +57,7 @@ EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
-"ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
+    "ab_set_detection_levels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
@@ -255,6 +255,11 @@ class RuntimeNet(_Net):
         _check(lib.ab_infer_tiled(self._h, _ptr(image), h, w, max_tile_w, max_tile_h, _ptr(g) if g is not None else None, ng,
                                   _ptr(labels), _ptr(blended) if blended is not None else None))
         return (labels, blended) if return_blended else labels
+
+    def set_detection_levels(self, levels: Optional[Sequence[float]]) -> None:
+        """annonet_infer()'s detection_levels (annonet_infer.cpp:187-239); None / empty switches the blob filter off"""
+        a = np.ascontiguousarray(levels if levels is not None else [], dtype=np.float64)
+        _check(lib.ab_set_detection_levels(self._h, _ptr(a) if a.size else None, int(a.size)))
 
     def infer_device(self, image_ptr: int, h: int, w: int, max_tile_w: int, max_tile_h: int, labels_ptr: int) -> None:
         _check(lib.ab_infer_tiled_device(self._h, C.c_void_p(image_ptr), h, w, max_tile_w, max_tile_h, None, 0, C.c_void_p(labels_ptr)))

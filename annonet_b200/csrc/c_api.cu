@@ -173,6 +173,15 @@ ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, in
     return guarded([&] { E(net).infer_tiled_host(image_hwc, h, w, max_tile_w, max_tile_h, gains, ngains, labels_host, blended_host); });
 }
 
+ab_status ab_set_detection_levels(ab_net* net, const double* levels, int n)
+{
+    return guarded([&] {
+        if (n < 0 || (n > 0 && !levels)) throw std::invalid_argument("bad detection levels");
+        for (int i = 0; i < n; ++i) if (!(levels[i] >= 0.0)) throw std::invalid_argument("detection levels must be >= 0 (annonet_infer.cpp:189)");
+        E(net).set_detection_levels(levels, n);
+    });
+}
+
 ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h, const double* gains,
                                 int ngains, void* labels_dev)
 {
@@ -275,11 +284,11 @@ ab_status ab_get_level_tensor(ab_net* net, int level, int gradient, float* out, 
     });
 }
 
-static ab_status layer_values(ab_net* net, int idx, bool grad, float* out, size_t cap, size_t* count)
+static ab_status layer_values(ab_net* net, int idx, int which, float* out, size_t cap, size_t* count)
 {
     return guarded([&] {
         std::vector<float> v;
-        E(net).layer_values(idx, grad, v);
+        E(net).layer_values(idx, which, v);
         if (count) *count = v.size();
         if (out) {
             if (cap < v.size()) throw std::invalid_argument("buffer too small");
@@ -288,8 +297,22 @@ static ab_status layer_values(ab_net* net, int idx, bool grad, float* out, size_
     });
 }
 
-ab_status ab_get_layer_gradient(ab_net* net, int idx, float* out, size_t cap, size_t* count) { return layer_values(net, idx, true, out, cap, count); }
-ab_status ab_get_layer_params(ab_net* net, int idx, float* out, size_t cap, size_t* count) { return layer_values(net, idx, false, out, cap, count); }
+ab_status ab_get_layer_gradient(ab_net* net, int idx, float* out, size_t cap, size_t* count) { return layer_values(net, idx, 1, out, cap, count); }
+ab_status ab_get_layer_params(ab_net* net, int idx, float* out, size_t cap, size_t* count) { return layer_values(net, idx, 0, out, cap, count); }
+ab_status ab_get_layer_momentum(ab_net* net, int idx, float* out, size_t cap, size_t* count) { return layer_values(net, idx, 2, out, cap, count); }
+ab_status ab_set_layer_momentum(ab_net* net, int idx, const float* v, size_t count) { return guarded([&] { E(net).set_layer_momentum(idx, v, count); }); }
+
+ab_status ab_get_layer_types(ab_net* net, int32_t* kinds, int cap, int* count)
+{
+    return guarded([&] {
+        const ab::NetModel& m = E(net).model();
+        if (count) *count = (int)m.layers.size();
+        if (kinds) {
+            if (cap < (int)m.layers.size()) throw std::invalid_argument("buffer too small");
+            for (size_t i = 0; i < m.layers.size(); ++i) kinds[i] = (int32_t)m.layers[i].type;
+        }
+    });
+}
 
 ab_status ab_gradient_arena(ab_net* net, void** grads_dev, size_t* count_floats)
 {

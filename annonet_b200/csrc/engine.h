@@ -75,6 +75,7 @@ public:
     // seams are exchanged with the neighbours and every rank ends up with the whole label map (engine_infer.cu)
     void infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                             uint16_t* labels_dev);
+    void set_detection_levels(const double* levels, int n) { detection_levels_.assign(levels, levels + (levels ? n : 0)); }
     void infer_tiled_host(const uint8_t* img_host, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                           uint16_t* labels_host, float* blended_host);
 
@@ -88,7 +89,8 @@ public:
     int last_n() const { return tn_; } int last_h() const { return th_; } int last_w() const { return tw_; }
     float* grads() const { return grads_.as<float>(); }
     float* params() const { return params_.as<float>(); }
-    void layer_values(int dlib_layer, bool gradient, std::vector<float>& out);  // dlib layout
+    void layer_values(int dlib_layer, int which, std::vector<float>& out);  // dlib layout; which: 0 parameters, 1 gradients, 2 sgd momentum
+    void set_layer_momentum(int dlib_layer, const float* v, size_t n);        // the solver state of a dnn_trainer sync file
     // all tensors of one resolution level after the last training step (activations or their gradients), NCHW fp32
     void level_values(int level, bool gradient, std::vector<float>& out, int dims[4]);
 
@@ -118,7 +120,7 @@ private:
     void tc_close_segment();
     std::unique_ptr<TcState> tc_;
 
-    int device_, precision_;
+    int device_, precision_, requested_precision_;   // precision_: what the loaded net actually runs on (load() may fall back to fp32)
     cudaStream_t stream_ = nullptr, comm_stream_ = nullptr, copy_stream_ = nullptr;
     cudaEvent_t ev_bucket_[8] = {}, ev_comm_done_ = nullptr, ev_stage_ = nullptr, ev_unstaged_ = nullptr;
     bool loaded_ = false;
@@ -135,7 +137,8 @@ private:
 
     // inference workspace
     Levels iw_;
-    DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_;
+    DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_, det_dev_, seeds_, blob_parent_, blob_keep_;
+    std::vector<double> detection_levels_;   // annonet_infer()'s detection_levels; empty or all zero: no blob filter
     int canvas_rows_ = 0, canvas_row0_ = 0;   // the blend canvas holds image rows [canvas_row0_, canvas_row0_ + canvas_rows_)
     void* pinned_ = nullptr; size_t pinned_bytes_ = 0;
     void* pinned(size_t bytes);

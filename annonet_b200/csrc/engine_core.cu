@@ -41,7 +41,7 @@ void nccl_unique_id(void* id128)
     std::memcpy(id128, &id, 128);
 }
 
-Engine::Engine(int device, int precision) : device_(device), precision_(precision)
+Engine::Engine(int device, int precision) : device_(device), precision_(precision), requested_precision_(precision)
 {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
@@ -101,7 +101,28 @@ void Engine::load(const NetModel& m)
     synchronize();
     model_ = m;
     plan_ = build_plan(model_);
-    tc_.reset();  // filter packs and launch descriptors of the h16 path belong to the old parameters
+    tc_.reset();  // filter packs and launch descriptors of the tensor-core path belong to the old parameters
+    // The tcgen05 kernels move channels in 16-byte (8 x fp16) vectors and keep a filter-gradient tile of at most 64 output
+    // channels; a width-scaled net (annonet_train --net-width-scaler, NetPimpl.cpp:73-130) with 4 / 6 / 10-channel layers or a
+    // net with more than 64 classes runs on the fp32 kernels of the same engine instead (same results within the tighter
+    // 1e-4 tolerance, slower) -- decided once per net, reported once.
+    precision_ = requested_precision_;
+    if (precision_ == 1) {
+        std::string why;
+        for (const ConvGroup& g : plan_.groups) {
+            if (g.dead) continue;
+            if (g.in_level >= 0 && (g.cin % 8 || g.in_c0 % 8)) why = "an input slice of " + std::to_string(g.cin) + " channels";
+            if (g.out_level >= 0 && (g.cout % 8 || g.out_c0 % 8 || g.cout > 64)) why = "a layer with " + std::to_string(g.cout) + " output channels";
+        }
+        for (int l = 0; l <= plan_.levels; ++l)
+            if (plan_.level_channels[l] % 8) why = "a level of " + std::to_string(plan_.level_channels[l]) + " channels";
+        if (plan_.class_count > 64) why = std::to_string(plan_.class_count) + " classes";
+        if (!why.empty()) {
+            precision_ = 0;
+            fprintf(stderr, "annonet_b200: this net has %s: running it on the fp32 kernels (the tensor-core path needs channel counts that are "
+                            "multiples of 8, at most 64 per layer, and at most 64 classes)\n", why.c_str());
+        }
+    }
     const size_t np = plan_.num_params;
     std::vector<float> hp(np, 0.f), lrm(np, 1.f), wdm(np, 1.f);
     running_off_.assign(plan_.groups.size(), 0);
@@ -185,7 +206,23 @@ NetModel Engine::snapshot(bool as_runtime)
     return out;
 }
 
-void Engine::layer_values(int dlib_layer, bool gradient, std::vector<float>& out)
+void Engine::set_layer_momentum(int dlib_layer, const float* v, size_t n)
+{
+    if (!loaded_) throw state_error("no net loaded");
+    if (dlib_layer < 0 || dlib_layer >= (int)plan_.layer_size.size() || plan_.layer_size[dlib_layer] != n)
+        throw std::invalid_argument("layer<" + std::to_string(dlib_layer) + ">: solver state size does not match the layer's parameters");
+    synchronize();
+    std::vector<float> raw(n);
+    for (const ConvGroup& g : plan_.groups) {
+        if (g.dlib_conv == dlib_layer) pack_filters(g, v, raw.data(), raw.data() + g.nweights());
+        else if (g.dlib_bn == dlib_layer) raw.assign(v, v + n);
+        else continue;
+        AB_CUDA(cudaMemcpy(mom_.as<float>() + plan_.layer_off[dlib_layer], raw.data(), n * 4, cudaMemcpyHostToDevice));
+        return;
+    }
+}
+
+void Engine::layer_values(int dlib_layer, int which, std::vector<float>& out)
 {
     if (!loaded_) throw state_error("no net loaded");
     if (dlib_layer < 0 || dlib_layer >= (int)plan_.layer_size.size() || plan_.layer_size[dlib_layer] == 0)
@@ -193,7 +230,8 @@ void Engine::layer_values(int dlib_layer, bool gradient, std::vector<float>& out
     synchronize();
     const size_t off = plan_.layer_off[dlib_layer], n = plan_.layer_size[dlib_layer];
     std::vector<float> raw(n);
-    AB_CUDA(cudaMemcpy(raw.data(), (gradient ? grads_ : params_).as<float>() + off, n * 4, cudaMemcpyDeviceToHost));
+    const DevBuf& arena = which == 0 ? params_ : which == 1 ? grads_ : mom_;
+    AB_CUDA(cudaMemcpy(raw.data(), arena.as<float>() + off, n * 4, cudaMemcpyDeviceToHost));
     out.resize(n);
     for (const ConvGroup& g : plan_.groups) {
         if (g.dlib_conv == dlib_layer) { unpack_filters(g, raw.data(), raw.data() + g.nweights(), out.data()); return; }

@@ -240,9 +240,19 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
     }
     // ---- argmax of the rows I own, straight into the caller's label map; then every rank broadcasts its strip
     const double* gd = upload_gains(gains_dev_, gains, ngains, K, stream_);
+    // detection levels (annonet_infer.cpp:187-239): seeds are found with the argmax, the blob filter runs on the whole map
+    bool detect = false;
+    for (double v : detection_levels_) detect = detect || v > 0.0;
+    const double* dd = nullptr;
+    if (detect) {
+        if ((int)detection_levels_.size() < K) throw std::invalid_argument("fewer detection levels than classes");
+        dd = upload_gains(det_dev_, detection_levels_.data(), (int)detection_levels_.size(), K, stream_);
+        seeds_.reserve((size_t)h * W);
+    }
     if (!me.empty()) {
         const long long n = (long long)(me.own1 - me.own0 + 1) * W;
-        k::argmax_labels(canvas_.as<float>() + (size_t)(me.own0 - me.f0) * W, (long long)plane, K, n, gd, labels_dev + (size_t)me.own0 * W, stream_);
+        k::argmax_labels(canvas_.as<float>() + (size_t)(me.own0 - me.f0) * W, (long long)plane, K, n, gd, labels_dev + (size_t)me.own0 * W, stream_,
+                         dd, detect ? seeds_.as<uint8_t>() + (size_t)me.own0 * W : nullptr);
     }
     if (world_ > 1) {
         nccl_->check(nccl_->GroupStart(), "ncclGroupStart");
@@ -250,8 +260,17 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
             if (bands[r].empty()) continue;
             uint16_t* p = labels_dev + (size_t)bands[r].own0 * W;
             nccl_->check(nccl_->Broadcast(p, p, (size_t)(bands[r].own1 - bands[r].own0 + 1) * W * 2, /*ncclUint8*/ 1, r, comm_, stream_), "ncclBroadcast");
+            if (detect) {
+                uint8_t* s = seeds_.as<uint8_t>() + (size_t)bands[r].own0 * W;
+                nccl_->check(nccl_->Broadcast(s, s, (size_t)(bands[r].own1 - bands[r].own0 + 1) * W, 1, r, comm_, stream_), "ncclBroadcast");
+            }
         }
         nccl_->check(nccl_->GroupEnd(), "ncclGroupEnd");
+    }
+    if (detect) {   // blobs cross band boundaries: every rank filters the whole (2 bytes per pixel) map it now holds
+        blob_parent_.reserve((size_t)h * W * sizeof(int));
+        blob_keep_.reserve((size_t)h * W);
+        k::filter_detections(labels_dev, seeds_.as<uint8_t>(), h, w, blob_parent_.as<int>(), blob_keep_.as<uint8_t>(), stream_);
     }
     AB_CUDA(cudaGetLastError());
 }

@@ -73,7 +73,8 @@ void Engine::tc_ensure_train(int n, int h, int w)
     T.fwd_packs_valid = false;
     tc_pack_forward_filters();
     const int K = plan_.class_count;
-    if (K > 8) throw std::invalid_argument("the tensor-core training path supports at most 8 classes in this build");
+    if (K > 64) throw std::invalid_argument("the tensor-core training path supports at most 64 classes (one 64-channel filter-gradient tile)");
+    const int Kp = (K + 7) / 8 * 8;   // the loss gradient as a [positions][Kp] fp16 tensor
     ensure_workspace(T.tw, plan_, n, h, w, true, true, true, stream_);     // activations: hi + lo halves
     ensure_workspace(T.tg, plan_, n, h, w, false, false, false, stream_);  // gradients: single fp16 values, loss-scaled
     T.tw.pool_arg.reserve(std::max<size_t>(T.tw.pool.bytes / 2, 256));
@@ -117,7 +118,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
     zero_reserve(T.dz, z_elems * 2);
     zero_reserve(T.dpool, dpool_elems * 2);
     zero_reserve(T.upx, upx_elems * 2);
-    zero_reserve(T.glogits16, (size_t)T.tw.geo[0].positions() * 8 * 2);
+    zero_reserve(T.glogits16, (size_t)T.tw.geo[0].positions() * Kp * 2);
     zero_reserve(T.bwd_packs, bwd_elems * 2);
     zero_reserve(T.train_packs, tp_elems * 2);
     T.sums.reserve(sizeof(double) * 2 * cmax);
@@ -188,7 +189,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
         // gradient at the conv output: dz (in z's place), the loss gradient, or the gradient slice itself
         const h16* dz; int dz_ctot, dz_c0, dz_c;
         if (g.dlib_bn >= 0) { dz = T.dz.as<h16>() + t.z_off; dz_ctot = g.cout; dz_c0 = 0; dz_c = g.cout; }
-        else if (g.out_level == -2) { dz = T.glogits16.as<h16>(); dz_ctot = 8; dz_c0 = 0; dz_c = 8; }
+        else if (g.out_level == -2) { dz = T.glogits16.as<h16>(); dz_ctot = Kp; dz_c0 = 0; dz_c = Kp; }
         else { dz = T.tg.level[ol].as<h16>(); dz_ctot = plan_.level_channels[ol]; dz_c0 = g.out_c0; dz_c = g.cout; }
 
         // filter gradient

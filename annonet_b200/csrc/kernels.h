@@ -95,8 +95,13 @@ void extract_tile(const uint8_t* img, int IH, int IW, int left, int top, float* 
 void loss_forward_backward(const float* logits, const void* wlabels, float* grad, int N, int K, int H, int W,
                            double* loss_sum, cudaStream_t st);
 // to_label (loss.h:2921-2969): argmax_k float(logit + gain), lowest index wins ties, all-NaN -> 65535
+// det_dev / seeds (optional): seeds[i] = 1 where label > 0 and plane[label] - plane[0] > det[label] - det[0]
+// (the detection seeds of annonet_infer.cpp:204-212)
 void argmax_labels(const float* planes, long long plane_stride, int K, long long npix, const double* gains_dev,
-                   uint16_t* labels, cudaStream_t st);
+                   uint16_t* labels, cudaStream_t st, const double* det_dev = nullptr, uint8_t* seeds = nullptr);
+// annonet_infer.cpp:214-239: blobs of equal non-zero labels (8-neighbourhood) without a seed are set to 0.
+// parent: h*w ints, keep: h*w bytes of scratch.
+void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st);
 // blend (annonet_infer.cpp:102-164): canvas[k, Y, X] (+)= t * logits[k, y, x]
 struct BlendArgs {
     const float* logits; int K, th, tw;        // tile logits [K][th][tw]

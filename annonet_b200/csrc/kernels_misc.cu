@@ -73,7 +73,8 @@ __global__ void __launch_bounds__(256) loss_kernel(const float* __restrict__ log
 }
 
 __global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ planes, const long long plane_stride, const int K,
-                                                     const long long npix, const double* __restrict__ gains, uint16_t* __restrict__ labels)
+                                                     const long long npix, const double* __restrict__ gains, uint16_t* __restrict__ labels,
+                                                     const double* __restrict__ det, uint8_t* __restrict__ seeds)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npix) return;
@@ -85,6 +86,14 @@ __global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ p
         if (v > best) { best = v; label = (uint16_t)k; }
     }
     labels[i] = label;
+    if (seeds) {   // detection seed (annonet_infer.cpp:204-212): the winner beats the clean class by more than its detection level
+        bool s = false;
+        if (label > 0 && label < K) {
+            const float clean = __ldg(planes + i), mine = __ldg(planes + (long long)label * plane_stride + i);
+            s = (double)(mine - clean) > det[label] - det[0];
+        }
+        seeds[i] = s ? 1 : 0;
+    }
 }
 
 __device__ __forceinline__ double ramp(long long c, long long first_possible, long long first_in, long long last_in, long long last_possible)
@@ -187,10 +196,10 @@ void loss_forward_backward(const float* logits, const void* wlabels, float* grad
 }
 
 void argmax_labels(const float* planes, long long plane_stride, int K, long long npix, const double* gains_dev, uint16_t* labels,
-                   cudaStream_t st)
+                   cudaStream_t st, const double* det_dev, uint8_t* seeds)
 {
     ProfScope ps(F_ARGMAX, 0, (4.0 * K + 2.0) * npix, st);
-    argmax_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(planes, plane_stride, K, npix, gains_dev, labels);
+    argmax_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(planes, plane_stride, K, npix, gains_dev, labels, det_dev, seeds);
     count_launch();
 }
 

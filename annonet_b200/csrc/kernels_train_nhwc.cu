@@ -433,10 +433,13 @@ __global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __res
     const int n = (int)(i / hw);
     const long long rem = i - n * hw;
     const int y = (int)(rem / W), x = (int)(rem - (long long)y * W);
-    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int k = 0; k < K && k < 8; ++k) f[k] = planes[((long long)n * K + k) * hw + rem] * scale;
     const long long pos = n * (long long)(H + 1) * (W + 1) + (long long)(y + 1) * (W + 1) + (x + 1);
-    st8(out + pos * 8, pack8(f));
+    const int Kp = (K + 7) / 8 * 8;
+    for (int k0 = 0; k0 < Kp; k0 += 8) {
+        float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int k = k0; k < K && k < k0 + 8; ++k) f[k - k0] = planes[((long long)n * K + k) * hw + rem] * scale;
+        st8(out + pos * Kp + k0, pack8(f));
+    }
 }
 
 __global__ void __launch_bounds__(256) upsample_zero_kernel(const h16* __restrict__ in, int in_ctot, int in_c0, int C8, int N, int h, int w,
@@ -557,7 +560,7 @@ void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* 
 
 void planes_to_nhwc8(const float* planes, int K, h16* out, const Geo& g, cudaStream_t st, float scale)
 {
-    if (K > 8) throw std::invalid_argument("planes_to_nhwc8: at most 8 planes");
+    if (K > 64) throw std::invalid_argument("planes_to_nhwc8: at most 64 planes");
     const long long n = (long long)g.N * g.H * g.W;
     k::ProfScope ps(k::F_PACK, 0, (4.0 * K + 16.0) * n, st);
     planes_to_nhwc8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(planes, K, out, g.N, g.H, g.W, scale);

@@ -184,7 +184,7 @@ void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st, 
 // max_pool_<3,3,2,2,0,0> gradient (cpu_dlib.cpp:1971-2017): the first maximum of a window in row-major order receives it; gin +=
 // (`arg` as written by maxpool_nhwc in the forward pass)
 void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
-// f32 planes [N][K][H][W] * scale -> h16 padded flat [positions][8] (channels >= K are zero)
+// f32 planes [N][K][H][W] * scale -> h16 padded flat [positions][K rounded up to 8] (channels >= K are zero), K <= 64
 void planes_to_nhwc8(const float* planes, int K, h16* out, const Geo& g, cudaStream_t st, float scale = 1.f);
 // out (fine geometry, dense [positions][C]) = zero-stuffed in: out[2i][2j] = in[i][j], 0 at the other pixels
 void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, cudaStream_t st);

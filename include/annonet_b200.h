@@ -137,6 +137,11 @@ ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, in
  * rank's rows only, zero elsewhere.) */
 ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, int max_tile_w, int max_tile_h,
                          const double* gains, int ngains, uint16_t* labels_host, float* blended_host);
+/* annonet_infer()'s detection_levels argument (annonet_infer.cpp:32-41,187-239; the CLI's -d option): with any level > 0
+ * the label map of every following ab_infer_tiled* call goes through the blob filter -- connected blobs of equal non-zero
+ * labels (dlib::label_connected_blobs, 8-neighbourhood) that contain no pixel with
+ * logit[label] - logit[0] > level[label] - level[0] are set to 0.  n = 0 switches it off. */
+ab_status ab_set_detection_levels(ab_net* net, const double* levels, int n);
 /* Same with image and labels resident in device memory (image_dev: h*w*3 u8, labels_dev: h*w u16). */
 ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,
                                 const double* gains, int ngains, void* labels_dev);
@@ -166,6 +171,17 @@ ab_status ab_get_level_tensor(ab_net* net, int level, int gradient, float* out, 
 /* parameter gradients of one dlib layer<idx> in dlib's layout (visit_layer_parameter_gradients, core.h:3806-3816) */
 ab_status ab_get_layer_gradient(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
 ab_status ab_get_layer_params(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
+/* The solver state of one layer: dlib::sgd's momentum tensor v (solvers.h:121-127, "sgd2") in dlib's layout -- what a
+ * dnn_trainer synchronization file stores per computational layer (trainer.h:931-964: serialize(devices[0]->solvers)). */
+ab_status ab_get_layer_momentum(ab_net* net, int dlib_layer_index, float* out, size_t capacity_floats, size_t* count);
+ab_status ab_set_layer_momentum(ab_net* net, int dlib_layer_index, const float* v, size_t count);
+/* kind of every dlib layer<i>, i = 0 (loss) .. num_layers-1 (input): the static layer list of NetStructure.h:172-299 as
+ * ab_layer_kind values; out may be NULL */
+typedef enum ab_layer_kind {
+    AB_LAYER_LOSS = 0, AB_LAYER_CON, AB_LAYER_CONT, AB_LAYER_BN, AB_LAYER_AFFINE, AB_LAYER_MISH, AB_LAYER_MAX_POOL,
+    AB_LAYER_CONCAT_PREV, AB_LAYER_CONCAT, AB_LAYER_TAG, AB_LAYER_INPUT
+} ab_layer_kind;
+ab_status ab_get_layer_types(ab_net* net, int32_t* kinds, int capacity, int* count);
 
 /* data-parallel training: flat gradient arena for the caller's/engine's all-reduce
  * (multi_device_tensor_averager, tensor_tools.h:1609-1736 -> NCCL) */

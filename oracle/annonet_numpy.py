@@ -619,6 +619,33 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
     return (labels, blended) if return_blended else labels
 
 
+def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels: Sequence[float]) -> np.ndarray:
+    """the detection-level blob filter of annonet_infer(), annonet_infer.cpp:187-239: a pixel is a SEED when its label is
+    non-zero and blended[label] - blended[0] (float) > detection_levels[label] - detection_levels[0] (double); connected blobs
+    of equal non-zero labels (dlib::label_connected_blobs with zero_pixels_are_background, neighbors_8, connected_if_equal)
+    that hold no seed are set to 0.  Connected components by scipy.ndimage.label with the full 3x3 structure, per label."""
+    from scipy import ndimage
+    det = np.asarray(detection_levels, dtype=np.float64)
+    if not np.any(det > 0):
+        return labels.copy()
+    k = blended.shape[0]
+    lab = labels.astype(np.int64)
+    mine = np.take_along_axis(blended, np.minimum(lab, k - 1)[None], axis=0)[0]
+    diff = (mine - blended[0]).astype(F32).astype(np.float64)
+    seeds = (labels > 0) & (labels < k) & (diff > det[np.minimum(lab, k - 1)] - det[0])
+    out = labels.copy()
+    for value in np.unique(labels):
+        if value == 0:
+            continue
+        comp, n = ndimage.label(labels == value, structure=np.ones((3, 3), dtype=bool))
+        if n == 0:
+            continue
+        has_seed = np.zeros(n + 1, dtype=bool)
+        has_seed[np.unique(comp[seeds & (comp > 0)])] = True
+        out[(comp > 0) & ~has_seed[comp]] = 0
+    return out
+
+
 def set_weights(labels: np.ndarray, class_weight: float, image_weight: float) -> np.ndarray:
     """set_weights, annonet_train.h:20-83.  labels u16 [H,W] -> f32 weights [H,W]."""
     nr, nc = labels.shape

@@ -9,7 +9,7 @@
 // comes out of dlib's CPU code.
 #include "dlib-dnn-pimpl-wrapper/NetPimpl.h"
 #include "dlib-dnn-pimpl-wrapper/NetStructure.h"
-#include "ref_io.h"
+#include "cli_io.h"
 
 #include <cstdlib>
 #include <fstream>

@@ -1,22 +1,18 @@
-// TEST INFRASTRUCTURE ONLY (oracle). Never linked into or called by the product path.
-//
-// `annonet_ref`: a headless command-line driver around the UNMODIFIED reference, compiled from
-// the sources where they lie under /root/reference (see oracle/Makefile).  It exists because
-// the stock CLIs cannot be built on this box (annonet_infer_main.cpp:22 pulls in X11 through
-// <dlib/gui_widgets.h>) and because parity needs raw tensors, not PNGs.  Every number it
-// prints or dumps is produced by the reference's own code, reached through the reference's
-// own boundary API:
+// A headless command-line driver written against the reference's OWN boundary API only:
 //   NetPimpl::TrainingNet / NetPimpl::RuntimeNet   dlib-dnn-pimpl-wrapper/NetPimpl.h:29-102
-//   annonet_infer()                                annonet_infer.cpp:32-240
+//   annonet_infer()                                annonet_infer.cpp:32-240 (unmodified source)
 //   set_weights()                                  annonet_train.h:20-83
 //   tiling::get_tiles()                            tiling/tiling.cpp:23-87
-// (ref_direct.cpp adds what the pimpl hides: pristine init, loss value, per-layer gradients.)
-//
+// It exists because the stock annonet_infer_main.cpp cannot be built on a headless box (it pulls in X11 through
+// <dlib/gui_widgets.h>) and because parity needs raw tensors, not PNGs.  The same file is compiled twice:
+//   shim/Makefile    -> shim/_build/annonet_cli : linked with shim/NetPimpl_b200.cpp + libannonet_b200.so  (the engine)
+//   oracle/Makefile  -> oracle/_ref/annonet_ref : linked with the reference's NetPimpl.cpp + dlib's CPU dnn code (the oracle),
+//                       with -DAB_WITH_REF_DIRECT adding the verbs that reach behind the pimpl (oracle/ref_direct.cpp)
 // All tensors travel as raw little-endian files; shapes are given on the command line.
 #include "annonet_infer.h"
 #include "annonet_train.h"
 #include "tiling/dlib-wrapper.h"
-#include "ref_io.h"
+#include "cli_io.h"
 
 #include <chrono>
 #include <cstring>
@@ -28,10 +24,12 @@
 #include <omp.h>
 #endif
 
+#ifdef AB_WITH_REF_DIRECT
 int ref_materialize(const std::string& in_path, const std::string& out_path, unsigned seed);
 int ref_grads(const std::string& net_path, const std::vector<NetPimpl::input_type>& images,
               const std::vector<NetPimpl::training_label_type>& labels, const std::string& out_prefix, bool dump_layers);
 int ref_forward_layers(const std::string& anet_path, const NetPimpl::input_type& image, const std::string& out_path);
+#endif
 
 namespace {
 
@@ -134,7 +132,9 @@ int main(int argc, char** argv) try
         t.Serialize(arg(5));
         return 0;
     }
+#ifdef AB_WITH_REF_DIRECT
     if (cmd == "materialize") return ref_materialize(arg(2), arg(3), static_cast<unsigned>(std::stoul(arg(4))));
+#endif
     if (cmd == "runtime") {
         // <net> <out_anet>   -- RuntimeNet::operator=(TrainingNet), NetPimpl.cpp:226-232
         NetPimpl::TrainingNet t;
@@ -147,7 +147,9 @@ int main(int argc, char** argv) try
         // <anet> <img> <H> <W> <out>
         const long h = std::stol(arg(4)), w = std::stol(arg(5));
         const auto imgs = load_images(arg(3), 1, h, w);
+#ifdef AB_WITH_REF_DIRECT
         if (cmd == "forward_layers") return ref_forward_layers(arg(2), imgs[0], arg(6));
+#endif
         NetPimpl::RuntimeNet net;
         net.Deserialize(arg(2));
         const dlib::tensor& out = net.Forward(imgs[0]);
@@ -196,7 +198,11 @@ int main(int argc, char** argv) try
     if (cmd == "grads") {
         // <net> <imgs> <labels.u16> <weights.f32> <N> <H> <W> <out_prefix> [layers]
         const long n = std::stol(arg(6)), h = std::stol(arg(7)), w = std::stol(arg(8));
+#ifdef AB_WITH_REF_DIRECT
         return ref_grads(arg(2), load_images(arg(3), n, h, w), load_labels(arg(4), arg(5), n, h, w), arg(9), argc > 10);
+#else
+        throw std::runtime_error("grads needs the reference's internals (oracle build only)");
+#endif
     }
     if (cmd == "train") {
         // <net> <imgs> <labels.u16> <weights.f32> <N> <H> <W> <lr> <steps> <out_net> [bn_window] [out_anet] [sync_file]
@@ -229,6 +235,7 @@ int main(int argc, char** argv) try
                   << ", \"learning_rate\": " << t.GetLearningRate() << "}" << std::endl;
         return 0;
     }
+#ifdef AB_WITH_REF_DIRECT
     if (cmd == "adam") {
         // <n> <steps> <lr> <wd> <beta1> <beta2> <params.f32> <grads.f32 (steps*n)> <out_params.f32>
         // dlib's own Adam arithmetic (tt::compute_adam_update -> cpu::compute_adam_update, cpu_dlib.cpp:704-743) applied the
@@ -249,6 +256,7 @@ int main(int argc, char** argv) try
         out.write(reinterpret_cast<const char*>(params.host()), n * 4);
         return 0;
     }
+#endif
     if (cmd == "set_weights") {
         // <labels.u16> <H> <W> <class_weight> <image_weight> <out_weights.f32>
         const long h = std::stol(arg(3)), w = std::stol(arg(4));
@@ -339,6 +347,6 @@ int main(int argc, char** argv) try
 }
 catch (const std::exception& e)
 {
-    std::cerr << "annonet_ref: " << e.what() << std::endl;
+    std::cerr << "annonet_cli: " << e.what() << std::endl;
     return 1;
 }

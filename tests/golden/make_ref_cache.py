@@ -26,3 +26,6 @@ if __name__ == "__main__":
     img = c.synth_image(np.random.default_rng(104), 700, 900)
     gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
     print("infer_700x900_k8_t512", c.ref_infer_outputs(anet8, img, 512, "infer_700x900_k8_t512", gains=gains)["labels"].shape, flush=True)
+    det = [0.0, 0.30, 0.25, 0.35, 0.40, 0.20, 0.30, 0.25]
+    out = c.ref_infer_outputs(anet8, img, 512, "infer_700x900_k8_t512_det", gains=gains, detection_levels=det)
+    print("infer_700x900_k8_t512_det: non-zero labels", int((out["labels"] > 0).sum()), flush=True)

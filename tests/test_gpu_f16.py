@@ -139,6 +139,36 @@ def test_f16_tiled_inference_8_classes_matches_reference_on_baseline_config2_cro
     assert _near_tie_only(labels, ref["labels"], scores, 2 * TOL)
 
 
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+def test_detection_level_blob_filter_matches_reference(ab, precision):
+    """annonet_infer() with detection levels (the CLI's -d): argmax -> seeds -> 8-connected blobs of equal labels -> blobs without
+    a seed are zeroed (annonet_infer.cpp:187-239), as CUDA union-find connected components on the device-resident label map.
+    (1) EXACT against the oracle's restatement applied to the engine's own blended logits and unfiltered labels -- isolates the
+    seed test + connected components from forward rounding; (2) against the reference binary's filtered label map: a blob
+    whose best pixel sits within the path's logit error of its detection level may flip as a whole, nothing else may."""
+    anet = ref_random_net(8, 6, training=False)
+    img = synth_image(np.random.default_rng(104), 700, 900)
+    gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
+    det = [0.0, 0.30, 0.25, 0.35, 0.40, 0.20, 0.30, 0.25]
+    ref = ref_infer_outputs(anet, img, 512, "infer_700x900_k8_t512_det", gains=gains, detection_levels=det)
+    # the oracle restatement reproduces the reference's own filtered map from the reference's own blended logits
+    unfiltered = ref_infer_outputs(anet, img, 512, "infer_700x900_k8_t512", gains=gains)
+    assert np.array_equal(on.filter_detections(unfiltered["labels"], ref["blended"], det), ref["labels"])
+    rt = ab.RuntimeNet(0, ab.AB_PRECISION_FP32 if precision == "fp32" else ab.AB_PRECISION_F16)
+    rt.Deserialize(anet)
+    plain, blended = rt.infer(img, 512, 512, gains=gains, return_blended=True)
+    rt.set_detection_levels(det)
+    filtered = rt.infer(img, 512, 512, gains=gains)
+    assert np.array_equal(filtered, on.filter_detections(plain, blended, det))
+    assert (filtered > 0).sum() < (plain > 0).sum()          # the filter removed something ...
+    assert (filtered > 0).sum() > 0                           # ... and kept something
+    agree = float(np.mean(filtered == ref["labels"]))
+    print(f"detection levels, {precision}: {int((plain > 0).sum())} -> {int((filtered > 0).sum())} labelled pixels; agrees with the reference on {agree:.5f}")
+    assert agree >= (0.9999 if precision == "fp32" else 0.995)
+    rt.set_detection_levels(None)
+    assert np.array_equal(rt.infer(img, 512, 512, gains=gains), plain)
+
+
 def test_f16_forward_matches_oracle(ab):
     rng = np.random.default_rng(17)
     rt = df.to_runtime(df.random_net(class_count=3, seed=21))

@@ -1,0 +1,117 @@
+"""The drop-in boundary exercised the way a user of the reference would: the reference's OWN, unmodified front ends
+(annonet_train_main.cpp; annonet_infer.cpp behind a headless driver) compiled against shim/NetPimpl_b200.cpp and linked to
+libannonet_b200.so (shim/Makefile), run on the GPU, and cross-checked with the reference build (oracle/_ref/annonet_ref):
+  * annonet_train on a synthetic anno dataset (PNG images + *_mask.png) -> annonet.dnn + dnn_trainer state file
+  * the reference's annonet_infer() over RuntimeNet::Forward of the engine == the reference's own result on the same net
+  * the dnn_trainer synchronization file (trainer.h:931-964) is interchangeable in both directions, solver state included"""
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import dlib_format as df
+from conftest import REF_BIN, ROOT, golden_bytes, golden_npz, have_ref_binary, rel_err, run_ref, synth_image
+from png_util import write_anno_dataset
+
+pytestmark = pytest.mark.gpu
+
+TRAIN_BIN = os.path.join(ROOT, "shim", "_build", "annonet_train")
+CLI_BIN = os.path.join(ROOT, "shim", "_build", "annonet_cli")
+needs_bins = pytest.mark.skipif(not (os.access(TRAIN_BIN, os.X_OK) and os.access(CLI_BIN, os.X_OK) and have_ref_binary()),
+                                reason="shim/_build/* or oracle/_ref/annonet_ref not built (make -C shim; make -C oracle)")
+
+
+def _run(cmd, cwd=None, env=None, timeout=900):
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run([str(c) for c in cmd], cwd=cwd, env=e, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, f"{cmd[0]} failed ({r.returncode}):\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}"
+    return r.stdout
+
+
+@needs_bins
+def test_reference_train_cli_over_the_engine_then_reference_infer_over_the_engine():
+    rng = np.random.default_rng(11)
+    with tempfile.TemporaryDirectory() as tmp:
+        data = os.path.join(tmp, "data")
+        os.makedirs(data)
+        write_anno_dataset(data, rng, 4, 300, 320, synth_image)
+        out = _run([TRAIN_BIN, data, "--minibatch-size", 4, "--max-total-steps", 8, "--input-dimension-multiplier", 1.0,
+                    "--initial-learning-rate", 0.05, "--save-interval", 4, "--data-loader-thread-count", 2, "--cached-image-count", 4],
+                   cwd=tmp, env={"AB_PRECISION": "1"})
+        assert "Now training" in out
+        assert os.path.exists(os.path.join(tmp, "annonet.dnn")) and os.path.exists(os.path.join(tmp, "annonet_trainer_state_file.dat"))
+        # annonet.dnn = serialize(json) << factor << serialize(anet bytes)   (annonet_train_main.cpp:557-565)
+        r = df.Reader(open(os.path.join(tmp, "annonet.dnn"), "rb").read())
+        json_classes, factor, anet_len = r.string(), r.float(), r.int()
+        anet = bytes(r.data[r.pos:r.pos + anet_len])
+        assert factor == 1.0 and len(anet) == anet_len and len(anet) > 9_000_000
+        p = lambda n: os.path.join(tmp, n)
+        open(p("anet.dnn"), "wb").write(anet)
+        img = synth_image(rng, 330, 290)
+        img.tofile(p("img.u8"))
+        # the reference's annonet_infer() (unmodified annonet_infer.cpp) tile by tile over the ENGINE's RuntimeNet::Forward ...
+        _run([CLI_BIN, "infer", p("anet.dnn"), p("img.u8"), 330, 290, 192, 192, p("mine.u16"), "-", "-", p("mine.f32")], env={"AB_PRECISION": "1"})
+        # ... and over the reference's own dlib CPU net
+        run_ref("infer", p("anet.dnn"), p("img.u8"), 330, 290, 192, 192, p("ref.u16"), "-", "-", p("ref.f32"))
+        mine, ref = np.fromfile(p("mine.u16"), np.uint16), np.fromfile(p("ref.u16"), np.uint16)
+        bm, br = np.fromfile(p("mine.f32"), np.float32).reshape(3, -1), np.fromfile(p("ref.f32"), np.float32).reshape(3, -1)
+        err, agree = rel_err(bm, br), float(np.mean(mine == ref))
+        print(f"annonet_train over the engine: 8 steps; annonet_infer() over the engine vs the reference: blended logits max-rel {err:.3e}, labels agree {agree:.5f}")
+        assert err <= 2e-2
+        top2 = np.sort(br, axis=0)[-2:]
+        assert np.all((top2[1] - top2[0])[mine != ref] < 4e-2 * np.abs(br).max())
+
+
+def _nets_equal(a, b, tol=0.0):
+    na, nb = df.parse_net(open(a, "rb").read()), df.parse_net(open(b, "rb").read())
+    worst = 0.0
+    for (i, la), (_, lb) in zip(na.param_layers(), nb.param_layers()):
+        worst = max(worst, float(np.abs(la["params"] - lb["params"]).max()))
+        if la["type"] == "bn":
+            worst = max(worst, float(np.abs(la["running_means"] - lb["running_means"]).max()))
+            assert la["num_updates"] == lb["num_updates"]
+    assert worst <= tol, worst
+    return na, nb
+
+
+@needs_bins
+def test_trainer_state_file_is_interchangeable_with_the_reference():
+    """dnn_trainer version-13 synchronization file: written by the reference and resumed by the engine, and the other way
+    round.  Resuming + 0 steps must give back the stored net exactly; resuming + 1 step must move the parameters like the
+    other implementation's resumed step does (which needs the stored sgd momentum)."""
+    t = golden_npz("train_inputs.npz")
+    with tempfile.TemporaryDirectory() as tmp:
+        p = lambda n: os.path.join(tmp, n)
+        open(p("net.dnn"), "wb").write(golden_bytes("net_small.dnn"))
+        n = 3
+        t["images"][:3 * n].tofile(p("i.u8")); t["labels"][:3 * n].tofile(p("l.u16")); t["weights"][:3 * n].astype(np.float32).tofile(p("w.f32"))
+        t["images"][2 * n:3 * n].tofile(p("i3.u8")); t["labels"][2 * n:3 * n].tofile(p("l3.u16")); t["weights"][2 * n:3 * n].astype(np.float32).tofile(p("w3.f32"))
+        eng = lambda *a: _run([CLI_BIN, *a], env={"AB_PRECISION": "0"})
+        ref = lambda *a: _run([REF_BIN, *a])
+        for writer, reader, tag in ((ref, eng, "reference -> engine"), (eng, ref, "engine -> reference")):
+            sync = p("state_" + tag[:3])
+            # two steps, state file written by the forced flush of GetRuntimeNet
+            writer("train", p("net.dnn"), p("i.u8"), p("l.u16"), p("w.f32"), n, 127, 127, 0.1, 2, p("w2.dnn"), 50, p("w2a.dnn"), sync)
+            assert os.path.exists(sync)
+            for who, name in ((writer, "ww"), (reader, "rr")):
+                # resume + 0 steps: the stored net comes back
+                who("train", p("net.dnn"), p("i3.u8"), p("l3.u16"), p("w3.f32"), n, 127, 127, 0.1, 0, p(name + "0.dnn"), "-", p(name + "0a.dnn"), sync)
+            _nets_equal(p("ww0.dnn"), p("w2.dnn"))
+            _nets_equal(p("rr0.dnn"), p("w2.dnn"))
+            # resume + 1 step on both sides from COPIES of the state (the step rewrites the file)
+            for who, name in ((writer, "ww"), (reader, "rr")):
+                s2 = sync + "_" + name
+                open(s2, "wb").write(open(sync, "rb").read())
+                who("train", p("net.dnn"), p("i3.u8"), p("l3.u16"), p("w3.f32"), n, 127, 127, 0.1, 1, p(name + "1.dnn"), "-", p(name + "1a.dnn"), s2)
+            base = df.parse_net(open(p("w2.dnn"), "rb").read())
+            a, b = df.parse_net(open(p("ww1.dnn"), "rb").read()), df.parse_net(open(p("rr1.dnn"), "rb").read())
+            worst = 0.0
+            for (i, l0), (_, la), (_, lb) in zip(base.param_layers(), a.param_layers(), b.param_layers()):
+                da, db = la["params"] - l0["params"], lb["params"] - l0["params"]
+                if np.abs(da).max() > 0:
+                    worst = max(worst, rel_err(db, da))
+            print(f"state file {tag}: resumed nets identical; one resumed step moves the parameters alike (max-rel {worst:.2e})")
+            assert worst < 2e-2
