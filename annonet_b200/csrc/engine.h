@@ -47,6 +47,13 @@ struct Hyper {
     double loss_scale = 0;         // fp16 path: 0 = automatic (a power of two near n*h*w/4)
 };
 
+// device tables of the bilinear resizes a geometry needs (one per resized join; plan.h resize_axis)
+struct ResizeTables {
+    DevBuf buf;
+    k::ResizeTab tab[8];
+    void build(const LevelDims& d, int levels, cudaStream_t st);
+};
+
 struct NcclApi;
 struct TcState;  // h16 tensor-core path: workspaces, packed filters, launch descriptors (engine_bf16.cu)
 
@@ -99,7 +106,7 @@ public:
 
 private:
     // workspaces
-    struct Levels { DevBuf buf[8]; LevelDims dims; int n = 0, h = 0, w = 0; };
+    struct Levels { DevBuf buf[8]; LevelDims dims; ResizeTables resize; int n = 0, h = 0, w = 0; };
     void ensure_infer_ws(int h, int w);
     void ensure_train_ws(int n, int h, int w);
     void run_inference_graph(int h, int w);
@@ -137,6 +144,7 @@ private:
 
     // inference workspace
     Levels iw_;
+    DevBuf i_up_, t_up_;   // the up-sampled tensor of a join that needs the bilinear resize (non-canonical input sizes)
     DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_, det_dev_, seeds_, blob_parent_, blob_keep_;
     std::vector<double> detection_levels_;   // annonet_infer()'s detection_levels; empty or all zero: no blob filter
     int canvas_rows_ = 0, canvas_row0_ = 0;   // the blend canvas holds image rows [canvas_row0_, canvas_row0_ + canvas_rows_)

@@ -31,6 +31,35 @@ void DevBuf::reserve(size_t n)
     bytes = n;
 }
 
+void ResizeTables::build(const LevelDims& d, int levels, cudaStream_t st)
+{
+    std::vector<int> ints;
+    std::vector<float> floats;
+    struct Off { size_t i, f; int oh, ow; } off[8] = {};
+    for (int l = 0; l < levels; ++l) {
+        if (!d.resized[l]) continue;
+        const ResizeAxis r = resize_axis(d.up_h[l], d.h[l], false), c = resize_axis(d.up_w[l], d.w[l], true);
+        off[l] = Off{ints.size(), floats.size(), d.h[l], d.w[l]};
+        ints.insert(ints.end(), r.lo.begin(), r.lo.end()); ints.insert(ints.end(), r.hi.begin(), r.hi.end());
+        ints.insert(ints.end(), c.lo.begin(), c.lo.end()); ints.insert(ints.end(), c.hi.begin(), c.hi.end());
+        floats.insert(floats.end(), r.frac.begin(), r.frac.end()); floats.insert(floats.end(), r.ifrac.begin(), r.ifrac.end());
+        floats.insert(floats.end(), c.frac.begin(), c.frac.end()); floats.insert(floats.end(), c.ifrac.begin(), c.ifrac.end());
+    }
+    if (ints.empty()) return;
+    buf.reserve(ints.size() * 4 + floats.size() * 4);
+    AB_CUDA(cudaMemcpyAsync(buf.p, ints.data(), ints.size() * 4, cudaMemcpyHostToDevice, st));
+    AB_CUDA(cudaMemcpyAsync((char*)buf.p + ints.size() * 4, floats.data(), floats.size() * 4, cudaMemcpyHostToDevice, st));
+    AB_CUDA(cudaStreamSynchronize(st));   // (the host vectors are locals)
+    const int* ip = buf.as<int>();
+    const float* fp = (const float*)((const char*)buf.p + ints.size() * 4);
+    for (int l = 0; l < levels; ++l) {
+        if (!d.resized[l]) continue;
+        const Off& o = off[l];
+        tab[l] = k::ResizeTab{ip + o.i, ip + o.i + o.oh, ip + o.i + 2 * o.oh, ip + o.i + 2 * o.oh + o.ow,
+                              fp + o.f, fp + o.f + o.oh, fp + o.f + 2 * o.oh, fp + o.f + 2 * o.oh + o.ow};
+    }
+}
+
 // ---- NCCL, resolved at run time from the process (torch bundles libnccl.so.2) -----------------
 
 void nccl_unique_id(void* id128)
@@ -185,6 +214,16 @@ NetModel Engine::snapshot(bool as_runtime)
     AB_CUDA(cudaMemcpy(hp.data(), params_.p, np * 4, cudaMemcpyDeviceToHost));
     if (!hr.empty()) AB_CUDA(cudaMemcpy(hr.data(), running_.p, hr.size() * 4, cudaMemcpyDeviceToHost));
     if (!num_updates_.empty()) AB_CUDA(cudaMemcpy(num_updates_.data(), nu_dev_.p, sizeof(unsigned long long) * num_updates_.size(), cudaMemcpyDeviceToHost));
+    // the batch statistics of the last forward pass: bn_ serializes its `means` / `invstds` members (layers.h:1428-1448), and
+    // dlib's next training pass asserts that they have the running statistics' dimensions (cpu_dlib.cpp:1087)
+    std::vector<float> hs;
+    if (stats_valid_ && t_stats_.p && !stats_off_.empty()) {
+        size_t n = 0;
+        for (size_t gi = 0; gi < plan_.groups.size(); ++gi)
+            if (plan_.groups[gi].dlib_bn >= 0) n = std::max(n, stats_off_[gi] + 2 * (size_t)plan_.groups[gi].cout);
+        hs.resize(n);
+        AB_CUDA(cudaMemcpy(hs.data(), t_stats_.p, n * 4, cudaMemcpyDeviceToHost));
+    }
     NetModel out = model_;
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
         const ConvGroup& g = plan_.groups[gi];
@@ -199,6 +238,11 @@ NetModel Engine::snapshot(bool as_runtime)
                 lb.running_variances.v.assign(hr.begin() + running_off_[gi] + g.cout, hr.begin() + running_off_[gi] + 2 * g.cout);
                 lb.num_updates = num_updates_[gi];
                 lb.window = window_[gi];
+                if (!hs.empty()) {   // [mean(C) | invstd(C)] of the last training forward pass, as [1, C, 1, 1] tensors
+                    for (HostTensor* t : {&lb.means, &lb.invstds}) { t->d[0] = 1; t->d[1] = g.cout; t->d[2] = 1; t->d[3] = 1; }
+                    lb.means.v.assign(hs.begin() + stats_off_[gi], hs.begin() + stats_off_[gi] + g.cout);
+                    lb.invstds.v.assign(hs.begin() + stats_off_[gi] + g.cout, hs.begin() + stats_off_[gi] + 2 * g.cout);
+                }
             }
         }
     }

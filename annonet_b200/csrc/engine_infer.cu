@@ -15,6 +15,11 @@ void Engine::ensure_infer_ws(int h, int w)
     const LevelDims d = level_dims(h, w, plan_.levels);
     for (int l = 0; l <= plan_.levels; ++l)
         iw_.buf[l].reserve((size_t)plan_.level_channels[l] * d.h[l] * d.w[l] * sizeof(float));
+    size_t up_max = 0;
+    for (const ConvGroup& g : plan_.groups)
+        if (g.is_cont && g.stride == 2 && d.resized[g.out_level]) up_max = std::max(up_max, (size_t)g.cout * d.up_h[g.out_level] * d.up_w[g.out_level]);
+    if (up_max) i_up_.reserve(up_max * sizeof(float));
+    iw_.resize.build(d, plan_.levels, stream_);
     i_x_.reserve((size_t)3 * h * w * sizeof(float));
     i_logits_.reserve((size_t)plan_.class_count * h * w * sizeof(float));
     iw_.dims = d;
@@ -46,7 +51,13 @@ void Engine::run_inference_graph(int h, int w)
         }
         a.wv.w = P + g.w_off;
         if (g.is_cont && g.stride == 2) {
-            up_forward(a.in, a.out, 1, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
+            if (d.resized[ol]) {   // concat_prev_ resizes the up-sampled tensor to the skip's size (layers.h:2438,2494-2521)
+                Slice tmp;
+                tmp.p = i_up_.as<float>(); tmp.sstride = (long long)g.cout * d.up_h[ol] * d.up_w[ol]; tmp.c0 = 0; tmp.C = g.cout;
+                up_forward(a.in, tmp, 1, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
+                resize_bilinear_nchw(tmp, d.up_h[ol], d.up_w[ol], a.out, 1, a.H, a.W, iw_.resize.tab[ol], stream_);
+            } else
+                up_forward(a.in, a.out, 1, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
         } else if (g.ksize == 3) {
             if (!g.is_cont) { a.wv.s_out = g.cin * 9; a.wv.s_in = 9; a.wv.flip = 0; }
             else { a.wv.s_out = 9; a.wv.s_in = g.cout * 9; a.wv.flip = 1; }
@@ -270,7 +281,9 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
     if (detect) {   // blobs cross band boundaries: every rank filters the whole (2 bytes per pixel) map it now holds
         blob_parent_.reserve((size_t)h * W * sizeof(int));
         blob_keep_.reserve((size_t)h * W);
-        k::filter_detections(labels_dev, seeds_.as<uint8_t>(), h, w, blob_parent_.as<int>(), blob_keep_.as<uint8_t>(), stream_);
+        // default: the reference's own seed lookup, quirk included (kernels_blobs.cu); AB_DETECTION_SEEDS=intended: same-pixel lookup
+        static const bool intended = getenv("AB_DETECTION_SEEDS") && std::string(getenv("AB_DETECTION_SEEDS")) == "intended";
+        k::filter_detections(labels_dev, seeds_.as<uint8_t>(), h, w, blob_parent_.as<int>(), blob_keep_.as<uint8_t>(), stream_, intended ? 0 : 1);
     }
     AB_CUDA(cudaGetLastError());
 }

@@ -103,6 +103,16 @@ void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bo
     if (ws.n == n && ws.h == h && ws.w == w && ws.split == split) return;
     const LevelDims d = level_dims(h, w, plan.levels);
     const size_t halves = split ? 2 : 1;
+    ws.dims = d;
+    size_t up_elems = 0;
+    for (const ConvGroup& g : plan.groups)
+        if (g.is_cont && g.stride == 2 && d.resized[g.out_level]) {
+            tc::Geo& ug = ws.up_geo[g.out_level];
+            ug.N = n; ug.H = d.up_h[g.out_level]; ug.W = d.up_w[g.out_level];
+            up_elems = std::max(up_elems, (size_t)ug.positions() * g.cout);
+        }
+    if (up_elems) ws.up_tmp.reserve(up_elems * halves * sizeof(h16));
+    ws.resize.build(d, plan.levels, st);
     for (int l = 0; l <= plan.levels; ++l) {
         ws.geo[l].N = n; ws.geo[l].H = d.h[l]; ws.geo[l].W = d.w[l];
         const size_t elems = (size_t)ws.geo[l].positions() * plan.level_channels[l];
@@ -167,6 +177,12 @@ void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup&
             L.mode = (mode == tc::OUT_BF16_ACCUM) ? tc::OUT_BF16_UP_ACCUM : tc::OUT_BF16_UP;
             L.par_a = l / 2; L.par_b = l % 2;
             L.out_S = ws.geo[ol].S(); L.out_P = ws.geo[ol].P();
+            if (ws.dims.resized[ol]) {   // into the dense temporary of the up-sampled size; run_up_resize() brings it to the level
+                const tc::Geo& ug = ws.up_geo[ol];
+                L.out = ws.up_tmp.p; L.out_ctot = g.cout; L.out_c0 = 0;
+                L.out_lo_off = ws.split ? (long long)ug.positions() * g.cout : 0;
+                L.out_S = ug.S(); L.out_P = ug.P();
+            }
         }
         // algorithmic work: the convolution's FLOPs (the three MMAs of a split chunk are an implementation cost, not work) and one
         // read of the input + one write of the output in their stored widths
@@ -175,6 +191,18 @@ void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup&
         const double out_b = (mode == tc::OUT_F32_NHWC || mode == tc::OUT_F32_NCHW) ? 4.0 : (dst_lo_off ? 4.0 : 2.0);
         L.bytes = px * ((ws.split ? 4.0 : 2.0) * g.cin + out_b * g.cout * (up ? 1.0 : 1.0));
     }
+}
+
+// after the launches of an `up` group whose join needs the bilinear resize: temporary -> the group's level slice
+void run_up_resize(const Plan& plan, const ConvGroup& g, const TcWorkspace& ws, cudaStream_t st)
+{
+    const int ol = g.out_level;
+    if (!(g.is_cont && g.stride == 2) || !ws.dims.resized[ol]) return;
+    const tc::Geo& ug = ws.up_geo[ol];
+    const tc::View out{ws.level[ol].as<h16>(), plan.level_channels[ol], g.out_c0, g.cout, ws.level_lo[ol]};
+    const k::ResizeTab& t = ws.resize.tab[ol];
+    const tc::ResizeTabDev td{t.top, t.bottom, t.left, t.right, t.tb, t.itb, t.lr, t.ilr};
+    tc::resize_bilinear_nhwc(ws.up_tmp.as<h16>(), ws.split ? (long long)ug.positions() * g.cout : 0, g.cout, ug, out, ws.geo[ol], td, st);
 }
 
 void Engine::tc_ensure_infer(int h, int w)
@@ -217,6 +245,7 @@ void Engine::tc_run_inference(int h, int w)
             tc::maxpool_nhwc(T.iw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.iw.geo[g.in_level],
                              T.iw.pool.as<h16>() + T.iw.pool_off[gi], T.iw.geo[g.out_level], stream_);
         for (const ConvLaunch& L : T.groups[gi].infer) tc::launch_conv(L, stream_);
+        run_up_resize(plan_, g, T.iw, stream_);
     }
     AB_CUDA(cudaGetLastError());
 }

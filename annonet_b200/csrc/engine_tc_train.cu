@@ -419,6 +419,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             t.fwd[0].stat_mish = g.has_mish && !g.bn_first;
         }
         for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, stream_);
+        if (g.out_level >= 0) run_up_resize(plan_, g, T.tw, stream_);
         if (fused_stats) t.fwd[0].stat_sums = nullptr;   // (the launch took its copy)
         if (g.dlib_bn >= 0) {
             const int mish_first = g.bn_first ? 0 : 1;
@@ -468,7 +469,9 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
     for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
         const ConvGroup& g = plan_.groups[gi];
         TcGroup& t = T.groups[gi];
-        if (!g.dead) {
+        // (a group reached only through a resized join gets no gradient in the reference, plan.h grad_blocked: its parameter
+        // gradients stay at the zeros the arena was filled with)
+        if (!g.dead && !grad_blocked(T.tw.dims, g)) {
             const int ol = g.out_level == -2 ? 0 : g.out_level;
             const Geo& geo = T.tw.geo[ol];
             const bool up = g.is_cont && g.stride == 2;

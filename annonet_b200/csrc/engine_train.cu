@@ -20,6 +20,11 @@ void Engine::ensure_train_ws(int n, int h, int w)
         tw_grad_.buf[l].reserve(bytes);
     }
     tw_act_.dims = tw_grad_.dims = d;
+    size_t up_max = 0;
+    for (const ConvGroup& g : plan_.groups)
+        if (g.is_cont && g.stride == 2 && d.resized[g.out_level]) up_max = std::max(up_max, (size_t)n * g.cout * d.up_h[g.out_level] * d.up_w[g.out_level]);
+    if (up_max) t_up_.reserve(up_max * sizeof(float));
+    tw_act_.resize.build(d, plan_.levels, stream_);
     tw_act_.n = tw_grad_.n = n; tw_act_.h = tw_grad_.h = h; tw_act_.w = tw_grad_.w = w;
     t_x_.reserve((size_t)n * 3 * h * w * 4);
     t_logits_.reserve((size_t)n * K * h * w * 4);
@@ -82,7 +87,12 @@ void Engine::forward_train(int n, int h, int w)
         else out = y;
 
         if (g.is_cont && g.stride == 2) {
-            up_forward(in, out, n, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
+            if (d.resized[ol]) {   // concat_prev_ resizes the up-sampled tensor to the skip's size (layers.h:2438,2494-2521)
+                Slice tmp = dense_slice(t_up_.as<float>(), g.cout, (long long)d.up_h[ol] * d.up_w[ol]);
+                up_forward(in, tmp, n, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
+                resize_bilinear_nchw(tmp, d.up_h[ol], d.up_w[ol], out, n, H, W, tw_act_.resize.tab[ol], stream_);
+            } else
+                up_forward(in, out, n, d.h[g.in_level], d.w[g.in_level], P + g.w_off, P + g.b_off, stream_);
         } else {
             ConvArgs a;
             a.N = n; a.H = H; a.W = W; a.out = out; a.bias = P + g.b_off; a.wv.w = P + g.w_off;
@@ -131,8 +141,9 @@ void Engine::backward_train(int n, int h, int w)
 
     for (int gi = (int)plan_.groups.size() - 1; gi >= 0; --gi) {
         const ConvGroup& g = plan_.groups[gi];
-        if (g.dead) {
-            // never consumed: dlib back-propagates an all-zero gradient, every parameter gradient is exactly 0
+        if (g.dead || grad_blocked(d, g)) {
+            // never consumed -- or reached only through a resized join, which the reference's backward pass does not cross
+            // (plan.h): dlib back-propagates an all-zero gradient, every parameter gradient is exactly 0
             fill_zero(G + g.w_off, (g.nweights() + g.cout + (g.dlib_bn >= 0 ? 2 * g.cout : 0)) * sizeof(float), stream_);
         } else {
             const int ol = g.out_level == -2 ? 0 : g.out_level;
@@ -234,7 +245,7 @@ void Engine::train_step_device(const uint8_t* imgs_dev, const void* labels_dev, 
     if (!loaded_) throw state_error("no net loaded");
     if (!model_.is_training) throw state_error("StartTraining needs a training net (net_type with bn_ layers)");
     AB_CUDA(cudaSetDevice(device_));
-    level_dims(h, w, plan_.levels);   // rejects non-canonical sizes
+    level_dims(h, w, plan_.levels);   // rejects inputs below the required input dimension
     if (precision_ == 1) { tc_train_step(imgs_dev, labels_dev, n, h, w, update); return; }   // AB_PRECISION_F16: tensor-core path
     ensure_train_ws(n, h, w);
     to_tensor(imgs_dev, t_x_.as<float>(), n, h, w, model_.avg[0], model_.avg[1], model_.avg[2], stream_);

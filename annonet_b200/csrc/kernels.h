@@ -100,8 +100,9 @@ void loss_forward_backward(const float* logits, const void* wlabels, float* grad
 void argmax_labels(const float* planes, long long plane_stride, int K, long long npix, const double* gains_dev,
                    uint16_t* labels, cudaStream_t st, const double* det_dev = nullptr, uint8_t* seeds = nullptr);
 // annonet_infer.cpp:214-239: blobs of equal non-zero labels (8-neighbourhood) without a seed are set to 0.
-// parent: h*w ints, keep: h*w bytes of scratch.
-void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st);
+// parent: h*w ints, keep: h*w bytes of scratch.  transposed_seeds: mirror the reference's (r, c) -> point(x = r, y = c) ->
+// blobs(y, x) seed lookup (annonet_infer.cpp:210,221) instead of the evidently intended same-pixel lookup.
+void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st, int transposed_seeds = 1);
 // blend (annonet_infer.cpp:102-164): canvas[k, Y, X] (+)= t * logits[k, y, x]
 struct BlendArgs {
     const float* logits; int K, th, tw;        // tile logits [K][th][tw]
@@ -126,6 +127,12 @@ void adam_step(float* w, const float* g, float* m, float* v, const float* lr_mul
 void loss_to_slot(const double* loss, float* slot, cudaStream_t st);
 void slot_to_loss(const float* slot, double* loss, int world, cudaStream_t st);
 void fill_zero(void* p, size_t bytes, cudaStream_t st);
+
+// concat_prev_'s bilinear resize of the up-sampled tensor to the skip's size (layers.h:2494-2521, cpu_dlib.cpp:1735-1762):
+// out[n, c, y, x] = ((wtl*tl + wtr*tr) + wbl*bl) + wbr*br with the source indices / fractions of plan.h resize_axis.
+// tab (device): ints top[oh] bottom[oh] left[ow] right[ow], then floats tb[oh] itb[oh] lr[ow] ilr[ow]
+struct ResizeTab { const int* top; const int* bottom; const int* left; const int* right; const float* tb; const float* itb; const float* lr; const float* ilr; };
+void resize_bilinear_nchw(const Slice& in, int ih, int iw, const Slice& out, int N, int oh, int ow, const ResizeTab& t, cudaStream_t st);
 
 }  // namespace k
 }  // namespace ab

@@ -59,14 +59,24 @@ __global__ void __launch_bounds__(256) blobs_merge_kernel(const uint16_t* __rest
     }
 }
 
-__global__ void __launch_bounds__(256) blobs_flatten_kernel(int* __restrict__ parent, const uint8_t* __restrict__ seeds, uint8_t* __restrict__ keep, long long n)
+// transposed: the reference stores a seed found at pixel (r, c) as dlib::point(x = r, y = c) and looks the blob up at
+// connected_blobs(point.y(), point.x()) = pixel (row c, col r) (annonet_infer.cpp:210,221).  Mirrored here: pixel (y, x) is
+// marked by the seed flag of pixel (x, y); lookups that would fall outside the image (the reference reads out of bounds
+// there) mark nothing.
+__global__ void __launch_bounds__(256) blobs_flatten_kernel(int* __restrict__ parent, const uint8_t* __restrict__ seeds, uint8_t* __restrict__ keep, int h,
+                                                            int w, int transposed)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= (long long)h * w) return;
     if (__ldcg(parent + i) < 0) return;
     const int r = find_root(parent, (int)i);
     parent[i] = r;          // (writes only shorten paths: concurrent readers still reach the same root)
-    if (seeds[i]) keep[r] = 1;
+    bool s;
+    if (transposed) {
+        const int y = (int)(i / w), x = (int)(i - (long long)y * w);
+        s = x < h && y < w && seeds[(long long)x * w + y];
+    } else s = seeds[i];
+    if (s) keep[r] = 1;
 }
 
 __global__ void __launch_bounds__(256) blobs_apply_kernel(uint16_t* __restrict__ labels, const int* __restrict__ parent, const uint8_t* __restrict__ keep, long long n)
@@ -80,7 +90,7 @@ __global__ void __launch_bounds__(256) blobs_apply_kernel(uint16_t* __restrict__
 
 }  // namespace
 
-void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st)
+void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st, int transposed_seeds)
 {
     const long long n = (long long)h * w;
     if (n >= (1ll << 31)) throw std::invalid_argument("filter_detections: image too large (pixel indices must fit 31 bits)");
@@ -88,7 +98,7 @@ void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int
     const unsigned grid = (unsigned)((n + 255) / 256);
     blobs_init_kernel<<<grid, 256, 0, st>>>(labels, parent, keep, n);
     blobs_merge_kernel<<<grid, 256, 0, st>>>(labels, parent, h, w);
-    blobs_flatten_kernel<<<grid, 256, 0, st>>>(parent, seeds, keep, n);
+    blobs_flatten_kernel<<<grid, 256, 0, st>>>(parent, seeds, keep, h, w, transposed_seeds);
     blobs_apply_kernel<<<grid, 256, 0, st>>>(labels, parent, keep, n);
     count_launch(4);
 }

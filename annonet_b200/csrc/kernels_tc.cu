@@ -433,7 +433,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 if (jpar > 0) break;
                 // next tile of this thread
                 c += step_c; r += step_r;
-                if (c >= P) { c -= P; ++r; }
+                // FLAT tiles walk on through the rows.  ROWS tiles keep their columns: a column at or beyond P (a partial last
+                // column tile) must stay invalid for every row -- wrapped into the next row it would be written a second time
+                // (harmless: the flat layout makes it the same value) and COUNTED a second time by the fused statistics.
+                if (!L.rows_mode && c >= P) { c -= P; ++r; }
                 while (r >= rows_per_sample) { r -= rows_per_sample; ++n; }
             }
             // this thread's TMEM reads of the buffer are complete (tcgen05.wait::ld in tmem_ld16): hand it back to the MMA warp

@@ -462,6 +462,42 @@ __global__ void __launch_bounds__(256) upsample_zero_kernel(const h16* __restric
     st8(out + (n * (long long)(Hf + 1) * (Wf + 1) + (long long)(y + 1) * (Wf + 1) + (x + 1)) * (C8 * 8) + cg * 8, v);
 }
 
+__global__ void __launch_bounds__(256) resize_nhwc_kernel(const h16* __restrict__ in, long long in_lo, int C8, int N, int ih, int iw, h16* __restrict__ out,
+                                                          int out_ctot, int out_c0, long long out_lo, int oh, int ow, const ResizeTabDev t)
+{
+    const long long total = (long long)N * oh * ow * C8;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int cg = (int)(i % C8);
+    long long p = i / C8;
+    const int x = (int)(p % ow); p /= ow;
+    const int y = (int)(p % oh);
+    const int n = (int)(p / oh);
+    const long long Si = (long long)(ih + 1) * (iw + 1), So = (long long)(oh + 1) * (ow + 1);
+    const int top = t.top[y], bottom = t.bottom[y], left = t.left[x], right = t.right[x];
+    const float wtl = __fmul_rn(t.itb[y], t.ilr[x]), wtr = __fmul_rn(t.itb[y], t.lr[x]), wbl = __fmul_rn(t.tb[y], t.ilr[x]), wbr = __fmul_rn(t.tb[y], t.lr[x]);
+    auto load = [&](int yy, int xx, float f[8]) {
+        const long long e = (n * Si + (long long)(yy + 1) * (iw + 1) + (xx + 1)) * (C8 * 8) + cg * 8;
+        unpack8(*reinterpret_cast<const BF8*>(in + e), f);
+        if (in_lo) {
+            float l[8];
+            unpack8(*reinterpret_cast<const BF8*>(in + in_lo + e), l);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] += l[k];
+        }
+    };
+    float tl[8], tr[8], bl[8], br[8], o[8];
+    load(top, left, tl); load(top, right, tr); load(bottom, left, bl); load(bottom, right, br);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        o[k] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(wtl, tl[k]), __fmul_rn(wtr, tr[k])), __fmul_rn(wbl, bl[k])), __fmul_rn(wbr, br[k]));
+    h16* op = out + (n * So + (long long)(y + 1) * (ow + 1) + (x + 1)) * out_ctot + out_c0 + cg * 8;
+    BF8 hi, lo;
+    split8(o, hi, lo);
+    st8(op, hi);
+    if (out_lo) st8(op + out_lo, lo);
+}
+
 __global__ void __launch_bounds__(256) pack_batched_kernel(const float* __restrict__ arena, h16* __restrict__ packs, const PackJob* __restrict__ jobs)
 {
     const PackJob& j = jobs[blockIdx.y];
@@ -573,6 +609,14 @@ void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, 
     const long long n = (long long)gf.N * gf.H * gf.W * (in.C / 8);
     k::ProfScope ps(k::F_PACK, 0, 2.0 * in.C * ((double)gc.N * gc.H * gc.W + (double)gf.N * gf.H * gf.W), st);
     upsample_zero_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in.p, in.ctot, in.c0, in.C / 8, gc.N, gc.H, gc.W, out);
+    k::count_launch();
+}
+
+void resize_bilinear_nhwc(const h16* in, long long in_lo_off, int C, const Geo& gi, const View& out, const Geo& go, const ResizeTabDev& t, cudaStream_t st)
+{
+    const long long n = (long long)go.N * go.H * go.W * (C / 8);
+    k::ProfScope ps(k::F_EW_BF16, 0, (in_lo_off ? 4.0 : 2.0) * C * ((double)gi.N * gi.H * gi.W + (double)go.N * go.H * go.W), st);
+    resize_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, in_lo_off, C / 8, go.N, gi.H, gi.W, out.p, out.ctot, out.c0, out.lo_off, go.H, go.W, t);
     k::count_launch();
 }
 

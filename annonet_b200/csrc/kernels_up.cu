@@ -145,5 +145,30 @@ void up_backward_data(const Slice& gout, const Slice& gin, int N, int h, int w, 
     count_launch();
 }
 
+namespace {
+__global__ void __launch_bounds__(256) resize_nchw_kernel(const Slice in, int ih, int iw, const Slice out, int oh, int ow, const ResizeTab t)
+{
+    const int n = blockIdx.z, c = blockIdx.y;
+    const float* s = in.p + (long long)n * in.sstride + (long long)(in.c0 + c) * ih * iw;
+    float* d = out.p + (long long)n * out.sstride + (long long)(out.c0 + c) * oh * ow;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < oh * ow; i += gridDim.x * blockDim.x) {
+        const int y = i / ow, x = i - y * ow;
+        const int top = t.top[y], bottom = t.bottom[y], left = t.left[x], right = t.right[x];
+        const float tb = t.tb[y], itb = t.itb[y], lr = t.lr[x], ilr = t.ilr[x];
+        const float tl = s[top * iw + left], tr = s[top * iw + right], bl = s[bottom * iw + left], br = s[bottom * iw + right];
+        d[i] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(itb, ilr), tl), __fmul_rn(__fmul_rn(itb, lr), tr)), __fmul_rn(__fmul_rn(tb, ilr), bl)),
+                         __fmul_rn(__fmul_rn(tb, lr), br));
+    }
+}
+}  // namespace
+
+void resize_bilinear_nchw(const Slice& in, int ih, int iw, const Slice& out, int N, int oh, int ow, const ResizeTab& t, cudaStream_t st)
+{
+    ProfScope ps(F_UP, 0, 4.0 * N * in.C * ((double)ih * iw + (double)oh * ow), st);
+    const unsigned gx = (unsigned)std::min((oh * ow + 255) / 256, 64);
+    resize_nchw_kernel<<<dim3(gx, in.C, N), 256, 0, st>>>(in, ih, iw, out, oh, ow, t);
+    count_launch();
+}
+
 }  // namespace k
 }  // namespace ab

@@ -1,6 +1,7 @@
 #include "plan.h"
 
 #include <algorithm>
+#include <cmath>
 #include <map>
 
 namespace ab {
@@ -22,11 +23,49 @@ LevelDims level_dims(int h, int w, int levels)
         d.h[n] = 1 + (d.h[n - 1] - 3) / 2;
         d.w[n] = 1 + (d.w[n - 1] - 3) / 2;
     }
-    for (int n = levels; n >= 1; --n)
-        if (2 * d.h[n] + 1 != d.h[n - 1] || 2 * d.w[n] + 1 != d.w[n - 1])
-            throw std::invalid_argument("input size " + std::to_string(h) + "x" + std::to_string(w) +
-                                        " is not of the form 64k+63 (RuntimeNet::GetRecommendedInputDimension)");
+    d.first_resized = -1;
+    for (int n = levels - 1; n >= 0; --n) {
+        d.up_h[n] = 2 * d.h[n + 1] + 1;
+        d.up_w[n] = 2 * d.w[n + 1] + 1;
+        d.resized[n] = d.up_h[n] != d.h[n] || d.up_w[n] != d.w[n];   // (by construction the difference is 0 or -1 per axis)
+        if (d.resized[n]) d.first_resized = n;
+    }
+    d.up_h[levels] = d.h[levels]; d.up_w[levels] = d.w[levels]; d.resized[levels] = false;
     return d;
+}
+
+ResizeAxis resize_axis(int n_in, int n_out, bool simd_columns)
+{
+    ResizeAxis a;
+    a.lo.assign(n_out, 0); a.hi.assign(n_out, 0); a.frac.assign(n_out, 0.f); a.ifrac.assign(n_out, 1.f);
+    const double scale = (n_in - 1) / (double)std::max(n_out - 1, 1);
+    int c = 0;
+    if (simd_columns) {
+        const double x0 = -4 * scale;
+        volatile float xv[4] = {(float)x0, (float)(x0 + scale), (float)(x0 + 2 * scale), (float)(x0 + 3 * scale)};
+        const float step = (float)(4 * scale);
+        while (true) {
+            int left[4];
+            for (int j = 0; j < 4; ++j) { xv[j] = xv[j] + step; left[j] = (int)xv[j]; }
+            if (left[3] + 1 >= n_in || c + 4 > n_out) break;
+            for (int j = 0; j < 4; ++j) {
+                a.lo[c + j] = left[j]; a.hi[c + j] = left[j] + 1;
+                volatile float f = xv[j] - (float)left[j];
+                a.frac[c + j] = f; a.ifrac[c + j] = 1.f - f;
+            }
+            c += 4;
+        }
+    }
+    double x = -scale + c * scale;
+    for (; c < n_out; ++c) {
+        x += scale;
+        const int left = (int)std::floor(x);
+        a.lo[c] = left; a.hi[c] = std::min(left + 1, n_in - 1);
+        a.frac[c] = (float)(x - left);
+        // rows: simd4f(1 - tb_frac) rounds the DOUBLE difference; tail columns: float lr_frac, then 1 - lr_frac
+        a.ifrac[c] = simd_columns ? 1.f - a.frac[c] : (float)(1.0 - (x - left));
+    }
+    return a;
 }
 
 Plan build_plan(const NetModel& net)

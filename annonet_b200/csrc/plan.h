@@ -47,11 +47,33 @@ struct Plan {
 Plan build_plan(const NetModel& net);
 
 // spatial size of each level for an h x w input: level 0 = input size, level n = 1+(level n-1 - 3)/2
-// (max_pool_<3,3,2,2>, layers.h:994-1012).  Also checks that the `up` path lands on the skip sizes
-// (cont_ out = 2*in+1, layers.h:521-535), i.e. h,w are "canonical" 64k+63 -- other sizes would need
-// concat_prev_'s +-1 bilinear resize (layers.h:2494-2521), which this build rejects.
-struct LevelDims { int h[8], w[8]; };
+// (max_pool_<3,3,2,2>, layers.h:994-1012).  The `up` path comes back with 2*in+1 (cont_<3,3,2,2,0,0>, layers.h:521-535):
+// up_h/up_w[n] is the size of the up-sampled tensor that joins level n.  For "canonical" sizes 64k+63 (what
+// RuntimeNet::GetRecommendedInputDimension hands the CLIs) it equals the level's size; an even-sized level comes back one
+// pixel short and concat_prev_ resizes it bilinearly (layers.h:2438,2494-2521): resized[n].
+// first_resized: the finest level with such a join (-1: none).  In the reference the gradient does NOT pass a resized join
+// (resize_if_needed hands the backward pass a temporary, layers.h:2452): every layer whose gradient arrives through it gets
+// exactly zero -- restated by the engines (grad_blocked) and checked against the compiled reference.
+struct LevelDims {
+    int h[8], w[8];
+    int up_h[8], up_w[8];
+    bool resized[8];
+    int first_resized;
+};
 LevelDims level_dims(int h, int w, int levels);
+// does group g's parameter gradient vanish because its only gradient path crosses a resized join?
+inline bool grad_blocked(const LevelDims& d, const ConvGroup& g)
+{
+    if (d.first_resized < 0) return false;
+    const int ol = g.out_level == -2 ? 0 : g.out_level;
+    return ol > d.first_resized || (g.is_cont && g.stride == 2 && ol == d.first_resized);
+}
+
+// source rows / columns and fractions of dlib's bilinear resize_image along one axis (image_transforms/interpolation.h:
+// 722-806), bit for bit: rows accumulate y in double; columns run in groups of four SSE floats (x_j = float(-4 s + j s),
+// advanced by float(4 s), left = trunc(x)) until a group's last `right` would leave the row, the rest in double
+struct ResizeAxis { std::vector<int> lo, hi; std::vector<float> frac, ifrac; };   // ifrac = 1 - frac as dlib rounds it
+ResizeAxis resize_axis(int n_in, int n_out, bool simd_columns);
 
 // dlib layout <-> arena layout for one group's filters (permutation along Cin)
 void pack_filters(const ConvGroup& g, const float* dlib_params, float* arena_w, float* arena_b);

@@ -186,6 +186,10 @@ void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st, 
 void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* gout_dense, const Geo& go, const View& gin, cudaStream_t st);
 // f32 planes [N][K][H][W] * scale -> h16 padded flat [positions][K rounded up to 8] (channels >= K are zero), K <= 64
 void planes_to_nhwc8(const float* planes, int K, h16* out, const Geo& g, cudaStream_t st, float scale = 1.f);
+// concat_prev_'s bilinear resize (layers.h:2494-2521; plan.h resize_axis): `in` (geometry gi, dense [positions][C], split when
+// in_lo_off != 0) -> channels of `out` (geometry go; both halves when out.lo_off != 0).  tab: device table as k::ResizeTab.
+struct ResizeTabDev { const int* top; const int* bottom; const int* left; const int* right; const float* tb; const float* itb; const float* lr; const float* ilr; };
+void resize_bilinear_nhwc(const h16* in, long long in_lo_off, int C, const Geo& gi, const View& out, const Geo& go, const ResizeTabDev& t, cudaStream_t st);
 // out (fine geometry, dense [positions][C]) = zero-stuffed in: out[2i][2j] = in[i][j], 0 at the other pixels
 void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, cudaStream_t st);
 

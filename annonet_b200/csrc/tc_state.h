@@ -40,6 +40,12 @@ struct TcWorkspace {
     DevBuf pool;               // pooled inputs of the transition_down groups, dense
     long long level_lo[8] = {0}, img_lo = 0;   // (a pooled tensor's lo half: positions * cin elements behind its hi half)
     DevBuf pool_arg;           // training: u8 index of the winning window element, same element offsets as `pool`
+    // non-canonical input sizes: a join whose up-sampled tensor comes back one pixel short (plan.h LevelDims::resized) gets it
+    // through this dense temporary [positions of up_geo][cout] (+ lo half when split) and the bilinear resize kernel
+    LevelDims dims;
+    tc::Geo up_geo[8];
+    DevBuf up_tmp;
+    ResizeTables resize;
     std::vector<size_t> pool_off;  // per group, in elements
 };
 
@@ -88,6 +94,7 @@ struct TcState {
 void setup_forward_launches(const Plan& plan, const ConvGroup& g, const TcGroup& t, const TcWorkspace& ws, const tc::h16* packs,
                             const size_t* pack_off, const float* P, std::vector<tc::ConvLaunch>& out, void* dst, int dst_ctot, int dst_c0,
                             long long dst_lo_off, int mode, int act);
+void run_up_resize(const Plan& plan, const ConvGroup& g, const TcWorkspace& ws, cudaStream_t st);
 void ensure_workspace(TcWorkspace& ws, const Plan& plan, int n, int h, int w, bool with_image, bool with_pool, bool split, cudaStream_t st);
 
 

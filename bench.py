@@ -439,6 +439,105 @@ def bench_infer_sharded(ab, device, precision, torch, dist, rank, world, size=16
             "mpix_per_s": size * size / (ms * 1e-3) / 1e6, "ms": ms, "n_gpus": world}
 
 
+# ---- BASELINE configs[4]: max-minibatch sweep at 1023 x 1023 crops against the GPU's HBM ----------------------------------
+SWEEP_CROP = 1023           # the 64w + 63 size the CLI feeds for "1024" (NetPimpl.cpp:246-285)
+
+
+def sweep_trial(args):
+    """one trial of the sweep, in its own process like the reference's script runs the CLI once per trial
+    (find_max_mini-batch_size.cmd:47-50: `%* -b N --max-total-steps=3`): 3 training steps of N crops; exit code 2 when the
+    engine reports CUDA out of memory (annonet_train_main.cpp:616-620 exits 2 on any exception), 3 on any other engine limit"""
+    import numpy as np
+    import torch
+    import annonet_b200 as ab
+    n, crop = args.sweep_trial, SWEEP_CROP
+    torch.cuda.set_device(0)
+    free0, total = torch.cuda.mem_get_info()
+    precision = ab.AB_PRECISION_F16 if args.precision == "f16" else ab.AB_PRECISION_FP32
+    net = ab.TrainingNet(0, precision)
+    net.Initialize(CLASSES, 1.0, 1, seed=1)
+    net.SetLearningRate(1e-3)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    try:
+        d_imgs = torch.randint(0, 256, (n, crop, crop, 3), dtype=torch.uint8, device="cuda", generator=g)
+        wl = np.zeros((crop, crop), dtype=ab.WLABEL)
+        yy, xx = np.mgrid[0:crop, 0:crop]
+        wl["label"] = ((yy // 16) + (xx // 16)) % CLASSES
+        wl["weight"] = 1.0
+        d_wl = torch.from_numpy(wl.view(np.uint8).reshape(crop, crop, 8)).cuda().unsqueeze(0).repeat(n, 1, 1, 1).contiguous()
+        stream = torch.cuda.ExternalStream(net.stream(), device=0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        net.train_step_device(d_imgs.data_ptr(), d_wl.data_ptr(), n, crop, crop)
+        loss = net.sync()
+        e0.record(stream)
+        for _ in range(2):
+            net.train_step_device(d_imgs.data_ptr(), d_wl.data_ptr(), n, crop, crop)
+        e1.record(stream)
+        loss = net.sync()
+        ms = e0.elapsed_time(e1) / 2
+    except (ab.CudaError, torch.OutOfMemoryError) as e:
+        oom = "out of memory" in str(e).lower()
+        print(json.dumps({"n": n, "ok": False, "why": "cuda out of memory" if oom else str(e)[:200]}))
+        return 2 if oom else 3
+    except ValueError as e:    # an engine limit other than memory (AB_ERR_ARGUMENT)
+        print(json.dumps({"n": n, "ok": False, "why": str(e)[:200]}))
+        return 3
+    free1, _ = torch.cuda.mem_get_info()
+    inputs = d_imgs.numel() + d_wl.numel()
+    print(json.dumps({"n": n, "ok": True, "ms_per_step": ms, "crops_per_s": n / (ms * 1e-3), "loss": loss, "hbm_used_bytes": int(free0 - free1),
+                      "engine_bytes_per_sample": (free0 - free1 - inputs) / n, "hbm_total_bytes": int(total)}))
+    return 0
+
+
+def sweep(args):
+    """find_max_mini-batch_size.cmd:1-69 restated: start at 100, double while the trial succeeds, then bisect between the
+    largest success and the smallest failure; every trial is its own process"""
+    trials = []
+
+    def trial(n):
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--sweep-trial", str(n), "--precision", args.precision],
+                           capture_output=True, text=True, timeout=1200)
+        line = {"n": n, "ok": False, "why": f"exit {r.returncode}: {r.stderr[-200:]}"}
+        for ln in r.stdout.strip().splitlines()[::-1]:
+            if ln.startswith("{"):
+                line = json.loads(ln)
+                break
+        line["exit_code"] = r.returncode
+        trials.append(line)
+        print(f"# trial N = {n}: {'ok' if r.returncode == 0 else 'FAILED (' + str(line.get('why')) + ')'}", file=sys.stderr, flush=True)
+        return r.returncode == 0
+
+    lo, hi, cur = 2, 0, 100
+    while True:
+        if trial(cur):
+            lo = cur
+            if hi == 0:
+                cur *= 2
+            elif lo + 0 >= hi:
+                break
+            else:
+                cur = (cur + hi + 1) // 2
+        else:
+            hi = cur - 1
+            cur = (lo + cur) // 2
+            if cur == lo or hi < lo:
+                break
+    best = max((t for t in trials if t.get("ok")), key=lambda t: t["n"], default=None)
+    first_fail = min((t for t in trials if not t.get("ok")), key=lambda t: t["n"], default=None)
+    ref_bytes_per_sample = 2 * 619.3 * 4 * SWEEP_CROP * SWEEP_CROP   # dlib keeps ~619 floats/px of activations + as many gradients (SURVEY §7)
+    total = best["hbm_total_bytes"] if best else 0
+    out = {"metric": "max_minibatch_1023x1023", "value": best["n"] if best else 0, "unit": "crops", "n_gpus": 1, "higher_is_better": True,
+           "dtype": "f16" if args.precision == "f16" else "f32", "data": "synthetic",
+           "config": {"workload": f"annonet_train, largest mini-batch of {SWEEP_CROP}x{SWEEP_CROP} crops that trains (3 steps) on one B200, {CLASSES} classes "
+                                  "(BASELINE configs[4]; bisection of find_max_mini-batch_size.cmd, one process per trial)"},
+           "best": best, "first_failure": first_fail, "limit": (first_fail or {}).get("why"),
+           "reference_equivalent": {"bytes_per_sample": ref_bytes_per_sample, "max_minibatch_at_this_hbm": int(total // ref_bytes_per_sample) if total else None,
+                                    "note": "dlib's executor keeps every layer output and gradient in fp32 (619 floats/px each, SURVEY §7): ~5.2 GB per 1023^2 sample"},
+           "trials": trials}
+    print(json.dumps(out))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -451,7 +550,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-infer", action="store_true", help="skip the secondary inference measurement")
     ap.add_argument("--no-infer16k", action="store_true", help="skip the sharded 16384^2 tiled inference (BASELINE configs[2])")
+    ap.add_argument("--sweep", action="store_true", help="BASELINE configs[4]: bisect the largest 1023x1023 mini-batch that fits the GPU")
+    ap.add_argument("--sweep-trial", type=int, default=0, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.sweep_trial:
+        return sweep_trial(args)
+    if args.sweep:
+        return sweep(args)
     if args.impl == "reference":
         return reference_arm(args)
     return own_arm(args)

@@ -140,7 +140,10 @@ ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, in
 /* annonet_infer()'s detection_levels argument (annonet_infer.cpp:32-41,187-239; the CLI's -d option): with any level > 0
  * the label map of every following ab_infer_tiled* call goes through the blob filter -- connected blobs of equal non-zero
  * labels (dlib::label_connected_blobs, 8-neighbourhood) that contain no pixel with
- * logit[label] - logit[0] > level[label] - level[0] are set to 0.  n = 0 switches it off. */
+ * logit[label] - logit[0] > level[label] - level[0] are set to 0.  n = 0 switches it off.
+ * The reference looks a seed found at pixel (r, c) up at pixel (row c, col r) (dlib::point(r, c) is x = r, y = c;
+ * annonet_infer.cpp:210,221); the engine mirrors that by default so that label maps match the reference's, and does the
+ * same-pixel lookup with the environment variable AB_DETECTION_SEEDS=intended. */
 ab_status ab_set_detection_levels(ab_net* net, const double* levels, int n);
 /* Same with image and labels resident in device memory (image_dev: h*w*3 u8, labels_dev: h*w u16). */
 ab_status ab_infer_tiled_device(ab_net* net, const void* image_dev, int h, int w, int max_tile_w, int max_tile_h,

@@ -133,6 +133,55 @@ def max_pool_bwd(gy: np.ndarray, arg: np.ndarray, in_hw: Tuple[int, int]) -> np.
     return dx
 
 
+def _resize_axis_tables(n_in: int, n_out: int, simd: bool):
+    """source index pairs and the fraction of dlib's bilinear resize_image along one axis (image_transforms/interpolation.h:
+    722-806).  Rows: y accumulates in double (y += y_scale), the fraction is later rounded to float.  Columns: groups of four
+    run in SSE floats -- x_j starts at float(-4*xs + j*xs) and is advanced by float(4*xs) per group, left = trunc(x) -- until a
+    group's right-most `right` index would leave the row; the remaining columns accumulate in double again."""
+    scale = (n_in - 1) / float(max(n_out - 1, 1))
+    lo, hi, frac = np.zeros(n_out, np.int64), np.zeros(n_out, np.int64), np.zeros(n_out, np.float64)
+    c = 0
+    if simd:
+        x0 = -4 * scale
+        xv = np.array([x0, x0 + scale, x0 + 2 * scale, x0 + 3 * scale], dtype=F32)
+        step = F32(4 * scale)
+        while True:
+            xv = (xv + step).astype(F32)
+            left = xv.astype(np.int32)            # simd4i(_x): cvttps -> truncation
+            right = left + 1
+            if right[3] >= n_in or c + 3 >= n_out + 3:   # (the reference's loop has no c bound of its own: `right` leaves the row first)
+                break
+            if c + 4 > n_out:
+                break
+            lr = (xv - left.astype(F32)).astype(F32)
+            lo[c:c + 4], hi[c:c + 4], frac[c:c + 4] = left, right, lr
+            c += 4
+    x = -scale + c * scale
+    for cc in range(c, n_out):
+        x += scale
+        left = int(math.floor(x))
+        lo[cc], hi[cc] = left, min(left + 1, n_in - 1)
+        frac[cc] = float(F32(x - left)) if simd else x - left
+    return lo, hi, frac
+
+
+def resize_bilinear(x: np.ndarray, out_h: int, out_w: int) -> np.ndarray:
+    """tt::resize_bilinear -> cpu::resize_bilinear -> dlib::resize_image(interpolate_bilinear) per channel plane,
+    cpu_dlib.cpp:1735-1762 and image_transforms/interpolation.h:700-806 (float pixels)."""
+    n, c, h, w = x.shape
+    top, bottom, tb = _resize_axis_tables(h, out_h, simd=False)
+    left, right, lr = _resize_axis_tables(w, out_w, simd=True)
+    tbf, lrf = tb.astype(F32), lr.astype(F32)
+    itb, ilr = (F32(1) - tbf).astype(F32), (F32(1) - lrf).astype(F32)
+    tl, tr = x[:, :, top][:, :, :, left], x[:, :, top][:, :, :, right]
+    bl, br = x[:, :, bottom][:, :, :, left], x[:, :, bottom][:, :, :, right]
+    wtl = (itb[:, None] * ilr[None, :]).astype(F32)
+    wtr = (itb[:, None] * lrf[None, :]).astype(F32)
+    wbl = (tbf[:, None] * ilr[None, :]).astype(F32)
+    wbr = (tbf[:, None] * lrf[None, :]).astype(F32)
+    return (((wtl * tl + wtr * tr).astype(F32) + wbl * bl).astype(F32) + wbr * br).astype(F32)
+
+
 def bn_inference(x, gamma, beta, rm, rv, eps):
     """batch_normalize_conv_inference, cpu_dlib.cpp:1008-1071."""
     invstd = (F32(1) / np.sqrt(rv + F32(eps))).astype(F32)
@@ -322,7 +371,11 @@ def forward(net: Net, x: np.ndarray, training: bool, update_running_stats: bool 
         elif t == "concat_prev":
             t2 = ctx.out[_res(L, _tagged(L, i, l["tag"]))]
             if xin.shape[2:] != t2.shape[2:]:
-                raise NotImplementedError("non-canonical input size: concat_prev_ would bilinearly resize (layers.h:2494-2521)")
+                # concat_prev_::resize_if_needed (layers.h:2438,2494-2521): the sub-network output is bilinearly resized to the
+                # tagged tensor's size (they differ by at most one pixel: an even-sized level pools to (s-1)/2 and comes back as s-1)
+                assert abs(xin.shape[2] - t2.shape[2]) <= 1 and abs(xin.shape[3] - t2.shape[3]) <= 1
+                xin = resize_bilinear(xin, t2.shape[2], t2.shape[3])
+                ctx.aux[("resized", i)] = True
             ctx.out[i] = np.concatenate([xin, t2], axis=1)
         elif t == "concat":
             ctx.out[i] = np.concatenate([ctx.out[_res(L, _tagged(L, i, tid))] for tid in l["tags"]], axis=1)
@@ -416,7 +469,13 @@ def backward(net: Net, ctx: Context, grad_logits: np.ndarray) -> Dict[int, np.nd
             add(i + 1, max_pool_bwd(gin, ctx.aux[i], xin.shape[2:]))
         elif t == "concat_prev":
             k1 = xin.shape[1]
-            add(i + 1, gin[:, :k1])
+            # Where the forward pass resized, the reference's backward pass adds this slice into a TEMPORARY
+            # (resize_if_needed returns resize_temp, layers.h:2452,2494-2518) that nobody reads: the sub-network's gradient input
+            # stays zero.  Restated as is -- the compiled reference's gradients confirm it (tests/test_gpu_resize.py).
+            if ctx.aux.get(("resized", i)):
+                add(i + 1, np.zeros_like(xin))
+            else:
+                add(i + 1, gin[:, :k1])
             add(_tagged(L, i, l["tag"]), gin[:, k1:])
         elif t == "concat":
             off = 0
@@ -619,11 +678,16 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
     return (labels, blended) if return_blended else labels
 
 
-def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels: Sequence[float]) -> np.ndarray:
+def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels: Sequence[float], transposed_seeds: bool = True) -> np.ndarray:
     """the detection-level blob filter of annonet_infer(), annonet_infer.cpp:187-239: a pixel is a SEED when its label is
     non-zero and blended[label] - blended[0] (float) > detection_levels[label] - detection_levels[0] (double); connected blobs
     of equal non-zero labels (dlib::label_connected_blobs with zero_pixels_are_background, neighbors_8, connected_if_equal)
-    that hold no seed are set to 0.  Connected components by scipy.ndimage.label with the full 3x3 structure, per label."""
+    that hold no seed are set to 0.  Connected components by scipy.ndimage.label with the full 3x3 structure, per label.
+
+    Reference quirk, restated as is: the seeds are stored as dlib::point(r, c) -- i.e. x = r, y = c (annonet_infer.cpp:210) -- and
+    looked up as connected_blobs(point.y(), point.x()) (:221), so the seed found at pixel (r, c) marks the blob at pixel
+    (row = c, col = r).  Out-of-range lookups (c >= rows or r >= cols, possible on non-square images) read past the matrix in
+    the reference; here they mark nothing.  transposed_seeds=False gives the evidently intended behaviour."""
     from scipy import ndimage
     det = np.asarray(detection_levels, dtype=np.float64)
     if not np.any(det > 0):
@@ -633,6 +697,14 @@ def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels:
     mine = np.take_along_axis(blended, np.minimum(lab, k - 1)[None], axis=0)[0]
     diff = (mine - blended[0]).astype(F32).astype(np.float64)
     seeds = (labels > 0) & (labels < k) & (diff > det[np.minimum(lab, k - 1)] - det[0])
+    if transposed_seeds:
+        h, w = labels.shape
+        m = min(h, w)
+        marked = np.zeros_like(seeds)
+        marked[:min(w, h), :min(h, w)] = False
+        t = seeds.T            # t[c, r] = seeds[r, c]
+        marked[:min(h, t.shape[0]), :min(w, t.shape[1])] = t[:h, :w]
+        seeds = marked
     out = labels.copy()
     for value in np.unique(labels):
         if value == 0:

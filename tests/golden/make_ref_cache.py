@@ -27,5 +27,14 @@ if __name__ == "__main__":
     gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
     print("infer_700x900_k8_t512", c.ref_infer_outputs(anet8, img, 512, "infer_700x900_k8_t512", gains=gains)["labels"].shape, flush=True)
     det = [0.0, 0.30, 0.25, 0.35, 0.40, 0.20, 0.30, 0.25]
-    out = c.ref_infer_outputs(anet8, img, 512, "infer_700x900_k8_t512_det", gains=gains, detection_levels=det)
-    print("infer_700x900_k8_t512_det: non-zero labels", int((out["labels"] > 0).sum()), flush=True)
+    img = c.synth_image(np.random.default_rng(105), 640, 640)
+    c.ref_infer_outputs(anet8, img, 512, "infer_640_k8_t512", gains=gains)
+    out = c.ref_infer_outputs(anet8, img, 512, "infer_640_k8_t512_det", gains=gains, detection_levels=det)
+    print("infer_640_k8_t512_det: non-zero labels", int((out["labels"] > 0).sum()), flush=True)
+    # non-canonical sizes (tests/test_gpu_resize.py)
+    small = c.golden_bytes("net_small.dnn")
+    for net, n, h, w, name in ((small, 2, 130, 150, "train_2x130x150_small"), (net3, 2, 256, 256, "train_2x256_k3")):
+        imgs, labs, wts = c.train_case(n, h, w, 3, seed=h + w)
+        c.ref_train_outputs(net, imgs, labs, wts, name)
+        c.oracle_train_outputs(net, imgs, labs, wts, name + "_exact")
+        print(name, flush=True)

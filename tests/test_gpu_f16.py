@@ -147,12 +147,12 @@ def test_detection_level_blob_filter_matches_reference(ab, precision):
     seed test + connected components from forward rounding; (2) against the reference binary's filtered label map: a blob
     whose best pixel sits within the path's logit error of its detection level may flip as a whole, nothing else may."""
     anet = ref_random_net(8, 6, training=False)
-    img = synth_image(np.random.default_rng(104), 700, 900)
+    img = synth_image(np.random.default_rng(105), 640, 640)   # square: the reference's transposed seed lookup stays in range
     gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
     det = [0.0, 0.30, 0.25, 0.35, 0.40, 0.20, 0.30, 0.25]
-    ref = ref_infer_outputs(anet, img, 512, "infer_700x900_k8_t512_det", gains=gains, detection_levels=det)
+    ref = ref_infer_outputs(anet, img, 512, "infer_640_k8_t512_det", gains=gains, detection_levels=det)
     # the oracle restatement reproduces the reference's own filtered map from the reference's own blended logits
-    unfiltered = ref_infer_outputs(anet, img, 512, "infer_700x900_k8_t512", gains=gains)
+    unfiltered = ref_infer_outputs(anet, img, 512, "infer_640_k8_t512", gains=gains)
     assert np.array_equal(on.filter_detections(unfiltered["labels"], ref["blended"], det), ref["labels"])
     rt = ab.RuntimeNet(0, ab.AB_PRECISION_FP32 if precision == "fp32" else ab.AB_PRECISION_F16)
     rt.Deserialize(anet)

@@ -46,7 +46,7 @@ def test_reference_train_cli_over_the_engine_then_reference_infer_over_the_engin
         # annonet.dnn = serialize(json) << factor << serialize(anet bytes)   (annonet_train_main.cpp:557-565)
         r = df.Reader(open(os.path.join(tmp, "annonet.dnn"), "rb").read())
         json_classes, factor, anet_len = r.string(), r.float(), r.int()
-        anet = bytes(r.data[r.pos:r.pos + anet_len])
+        anet = bytes(r.d[r.pos:r.pos + anet_len])
         assert factor == 1.0 and len(anet) == anet_len and len(anet) > 9_000_000
         p = lambda n: os.path.join(tmp, n)
         open(p("anet.dnn"), "wb").write(anet)
@@ -86,26 +86,28 @@ def test_trainer_state_file_is_interchangeable_with_the_reference():
     with tempfile.TemporaryDirectory() as tmp:
         p = lambda n: os.path.join(tmp, n)
         open(p("net.dnn"), "wb").write(golden_bytes("net_small.dnn"))
-        n = 3
-        t["images"][:3 * n].tofile(p("i.u8")); t["labels"][:3 * n].tofile(p("l.u16")); t["weights"][:3 * n].astype(np.float32).tofile(p("w.f32"))
+        n, hw = 2, 191
+        t["images"][:2 * n].tofile(p("i.u8")); t["labels"][:2 * n].tofile(p("l.u16")); t["weights"][:2 * n].astype(np.float32).tofile(p("w.f32"))
         t["images"][2 * n:3 * n].tofile(p("i3.u8")); t["labels"][2 * n:3 * n].tofile(p("l3.u16")); t["weights"][2 * n:3 * n].astype(np.float32).tofile(p("w3.f32"))
+        for f in ("i0.u8", "l0.u16", "w0.f32"):
+            open(p(f), "wb").close()   # resume + 0 steps: no samples
         eng = lambda *a: _run([CLI_BIN, *a], env={"AB_PRECISION": "0"})
         ref = lambda *a: _run([REF_BIN, *a])
         for writer, reader, tag in ((ref, eng, "reference -> engine"), (eng, ref, "engine -> reference")):
             sync = p("state_" + tag[:3])
             # two steps, state file written by the forced flush of GetRuntimeNet
-            writer("train", p("net.dnn"), p("i.u8"), p("l.u16"), p("w.f32"), n, 127, 127, 0.1, 2, p("w2.dnn"), 50, p("w2a.dnn"), sync)
+            writer("train", p("net.dnn"), p("i.u8"), p("l.u16"), p("w.f32"), n, hw, hw, 0.1, 2, p("w2.dnn"), 50, p("w2a.dnn"), sync)
             assert os.path.exists(sync)
             for who, name in ((writer, "ww"), (reader, "rr")):
                 # resume + 0 steps: the stored net comes back
-                who("train", p("net.dnn"), p("i3.u8"), p("l3.u16"), p("w3.f32"), n, 127, 127, 0.1, 0, p(name + "0.dnn"), "-", p(name + "0a.dnn"), sync)
+                who("train", p("net.dnn"), p("i0.u8"), p("l0.u16"), p("w0.f32"), n, hw, hw, 0.1, 0, p(name + "0.dnn"), "-", p(name + "0a.dnn"), sync)
             _nets_equal(p("ww0.dnn"), p("w2.dnn"))
             _nets_equal(p("rr0.dnn"), p("w2.dnn"))
             # resume + 1 step on both sides from COPIES of the state (the step rewrites the file)
             for who, name in ((writer, "ww"), (reader, "rr")):
                 s2 = sync + "_" + name
                 open(s2, "wb").write(open(sync, "rb").read())
-                who("train", p("net.dnn"), p("i3.u8"), p("l3.u16"), p("w3.f32"), n, 127, 127, 0.1, 1, p(name + "1.dnn"), "-", p(name + "1a.dnn"), s2)
+                who("train", p("net.dnn"), p("i3.u8"), p("l3.u16"), p("w3.f32"), n, hw, hw, 0.1, 1, p(name + "1.dnn"), "-", p(name + "1a.dnn"), s2)
             base = df.parse_net(open(p("w2.dnn"), "rb").read())
             a, b = df.parse_net(open(p("ww1.dnn"), "rb").read()), df.parse_net(open(p("rr1.dnn"), "rb").read())
             worst = 0.0
