@@ -178,8 +178,14 @@ def test_adam_steps_match_the_oracle_solver(ab, precision):
         net.sync()
         mine = df.parse_net(net.Serialize())
         for (i, a), (_, b) in zip(mine.param_layers(), onet.param_layers()):
-            # Adam's update is -alpha * m / (sqrt(v) + eps): where |g| ~ eps the quotient amplifies the last bits of g
-            assert np.max(np.abs(a["params"].reshape(-1) - b["params"].reshape(-1))) <= 2e-3 * 0.01 + 1e-6 * np.abs(b["params"]).max(), f"step {step} layer<{i}>"
+            # Adam's first steps move every parameter by ~lr * sign(g) whatever |g|: where the gradient is rounding noise (a conv
+            # bias in front of a batch norm has an exactly zero gradient; the engines' reductions use atomics, so that noise differs
+            # from run to run) the SIGN is noise too.  Compare where the gradient is above the noise, bound the step elsewhere.
+            g = np.abs(grads[i].reshape(-1))
+            solid = g > 1e-3 * g.max()
+            d = np.abs(a["params"].reshape(-1) - b["params"].reshape(-1))
+            assert d[solid].max() <= 2e-3 * 0.01 + 1e-6 * np.abs(b["params"]).max(), f"step {step} layer<{i}>"
+            assert d.max() <= 8 * 0.01, f"step {step} layer<{i}>: an Adam step is bounded by a few learning rates ((1 - b1) / sqrt(1 - b2) = 3.2)"
         # continue from the ENGINE's parameters so that rounding differences do not compound across steps
         for (i, a), (_, b) in zip(mine.param_layers(), onet.param_layers()):
             b["params"] = a["params"].copy()
