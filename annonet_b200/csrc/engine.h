@@ -129,6 +129,11 @@ private:
 
     int device_, precision_, requested_precision_;   // precision_: what the loaded net actually runs on (load() may fall back to fp32)
     cudaStream_t stream_ = nullptr, comm_stream_ = nullptr, copy_stream_ = nullptr;
+    // side stream of the training step: work that is off the critical path of the layer chain (filter gradients, the never
+    // consumed "dead" layers) runs there, next to the small launches of the coarse levels that leave most SMs idle
+    cudaStream_t side_stream_ = nullptr;
+    cudaEvent_t ev_fork_[32] = {}, ev_join_ = nullptr;
+    int fork_slot_ = 0;
     cudaEvent_t ev_bucket_[8] = {}, ev_comm_done_ = nullptr, ev_stage_ = nullptr, ev_unstaged_ = nullptr;
     bool loaded_ = false;
     NetModel model_;  // host copy of the structure (+ parameters as loaded; device is authoritative after load)

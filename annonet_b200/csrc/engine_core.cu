@@ -83,6 +83,9 @@ Engine::Engine(int device, int precision) : device_(device), precision_(precisio
     AB_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
     AB_CUDA(cudaStreamCreateWithFlags(&comm_stream_, cudaStreamNonBlocking));
     AB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    AB_CUDA(cudaStreamCreateWithFlags(&side_stream_, cudaStreamNonBlocking));
+    for (auto& ev : ev_fork_) AB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    AB_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
     for (auto& ev : ev_bucket_) AB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     AB_CUDA(cudaEventCreateWithFlags(&ev_comm_done_, cudaEventDisableTiming));
     AB_CUDA(cudaEventCreateWithFlags(&ev_stage_, cudaEventDisableTiming));
@@ -104,6 +107,9 @@ Engine::~Engine()
     if (loss_host_) cudaFreeHost(loss_host_);
     if (comm_stream_) cudaStreamDestroy(comm_stream_);
     if (copy_stream_) cudaStreamDestroy(copy_stream_);
+    if (side_stream_) cudaStreamDestroy(side_stream_);
+    for (auto& ev : ev_fork_) if (ev) cudaEventDestroy(ev);
+    if (ev_join_) cudaEventDestroy(ev_join_);
     if (stream_) cudaStreamDestroy(stream_);
 }
 

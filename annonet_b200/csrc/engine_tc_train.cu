@@ -91,9 +91,9 @@ void Engine::tc_ensure_train(int n, int h, int w)
         TcGroup& t = T.groups[gi];
         const int ol = g.out_level == -2 ? 0 : g.out_level;
         cmax = std::max(cmax, g.cout);
-        for (int l = 0; l < t.nlaunch; ++l) {   // split forward packs [hi | hi | lo]
+        for (int l = 0; l < t.nlaunch; ++l) {   // split forward packs: hi and lo filters side by side along N
             t.train_pack_off[l] = tp_elems;
-            tp_elems += (3 * tc::packed_filter_elems(g.in_level < 0 ? 8 : g.cin, t.npad, t.fwd_ntaps[l]) + 511) / 512 * 512;
+            tp_elems += (2 * tc::packed_filter_elems(g.in_level < 0 ? 8 : g.cin, t.npad, t.fwd_ntaps[l]) + 511) / 512 * 512;
         }
         if (g.dlib_bn >= 0) {
             stats_off_[gi] = stt; stt += 2 * (size_t)g.cout;
@@ -122,6 +122,7 @@ void Engine::tc_ensure_train(int n, int h, int w)
     zero_reserve(T.bwd_packs, bwd_elems * 2);
     zero_reserve(T.train_packs, tp_elems * 2);
     T.sums.reserve(sizeof(double) * 2 * cmax);
+    T.sums_side.reserve(sizeof(double) * 2 * cmax);
     T.bias_tmp.reserve(sizeof(float) * 256);
     T.wscratch.reserve(tc::wgrad_tc_scratch_floats() * 4);
     t_stats_.reserve(std::max<size_t>(stt, 1) * 4);
@@ -138,9 +139,9 @@ void Engine::tc_ensure_train(int n, int h, int w)
             j.w_off = (long long)g.w_off; j.packed_off = (long long)t.train_pack_off[l];
             j.sn = g.is_cont ? kk : (long long)g.cin * kk; j.sk = g.is_cont ? (long long)g.cout * kk : kk;
             j.nreal = g.cout; j.npad = t.npad; j.kreal = g.cin; j.kp = tc::padded_k(g.in_level < 0 ? 8 : g.cin); j.ntaps = t.fwd_ntaps[l];
-            j.parts = 3;
+            j.parts = 2;
             for (int i = 0; i < j.ntaps; ++i) j.tapmap[i] = t.fwd_tapmap[l][i];
-            T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp * 3);
+            T.max_pack_elems = std::max(T.max_pack_elems, j.ntaps * j.npad * j.kp * 2);
             jobs.push_back(j);
         }
     }
@@ -218,6 +219,11 @@ void Engine::tc_ensure_train(int n, int h, int w)
             }
 
         tc::setup_wgrad_tc(t.wgrad_tc, wj, T.wscratch.as<float>());
+        if (up) {   // algorithmic work of the stride-2 cont_: its input lives on the COARSE grid (the zero-stuffed copy is an implementation detail)
+            const double pxf = (double)wj.g.N * wj.g.H * wj.g.W;
+            t.wgrad_tc.flops *= 0.25;
+            t.wgrad_tc.bytes = 2.0 * pxf * (g.cin * 0.25 + g.cout);
+        }
 
         // backward-data
         if (g.in_level < 0) continue;
@@ -393,6 +399,26 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
 
     tc::image_to_nhwc(imgs_dev, h, w, 0, 0, T.tw.img.as<h16>(), T.tw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_, T.tw.img_lo);
 
+    // Side stream: work off the critical path of the layer chain -- filter gradients (only the optimizer needs them), the dead
+    // layers -- runs next to it; the chain's launches at the coarse levels occupy a few SMs each.  Forks and joins are event
+    // dependencies, captured into the step's CUDA graph as parallel branches.
+    static const bool no_side = getenv("AB_NO_SIDE") != nullptr;
+    bool side_busy = false;
+    auto fork_side = [&]() -> cudaStream_t {
+        if (no_side || k::prof_enabled()) return stream_;
+        cudaEvent_t ev = ev_fork_[fork_slot_++ % 32];
+        AB_CUDA(cudaEventRecord(ev, stream_));
+        AB_CUDA(cudaStreamWaitEvent(side_stream_, ev, 0));
+        side_busy = true;
+        return side_stream_;
+    };
+    auto join_side = [&]() {
+        if (!side_busy) return;
+        AB_CUDA(cudaEventRecord(ev_join_, side_stream_));
+        AB_CUDA(cudaStreamWaitEvent(stream_, ev_join_, 0));
+        side_busy = false;
+    };
+
     // ---- forward (batch-norm training mode)
     // The two reduction passes (bn statistics, bn backward sums) walk the positions downwards: their producers walked upwards, so
     // the last ~100 MB they wrote are still in the 126 MB L2, and the apply pass that follows (upwards) starts where the
@@ -404,45 +430,49 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         if (g.dead && hyper.skip_dead_layers) continue;
         const int ol = g.out_level == -2 ? 0 : g.out_level;
         const Geo& geo = T.tw.geo[ol];
+        // dead layers (computed, never consumed: NetStructure.h:41-55) only feed their own running statistics: side stream
+        cudaStream_t fs = g.dead ? fork_side() : stream_;
+        double* sums = fs == stream_ ? T.sums.as<double>() : T.sums_side.as<double>();
         if (g.pool_input)
             tc::maxpool_nhwc(T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
-                             T.tw.pool.as<h16>() + T.tw.pool_off[gi], geo, stream_, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi],
+                             T.tw.pool.as<h16>() + T.tw.pool_off[gi], geo, fs, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi],
                              T.tw.level_lo[g.in_level], geo.positions() * g.cin);
         // batch statistics ride in the conv epilogue where one 16-channel block is the whole output (the full-resolution layers):
         // saves the pass that re-reads z
         static const bool no_fused_stats = getenv("AB_NO_FUSED_STATS") != nullptr;
         const bool fused_stats = g.dlib_bn >= 0 && !no_fused_stats && t.fwd.size() == 1 && t.fwd[0].mode == tc::OUT_F32_NHWC &&
-                                 t.fwd[0].nblk == 16 && t.fwd[0].npad_total == 16;
+                                 t.fwd[0].nblk == 16 * t.fwd[0].nsum && t.fwd[0].npad_total == 16 * t.fwd[0].nsum;
         if (fused_stats) {
-            k::fill_zero(T.sums.p, sizeof(double) * 2 * g.cout, stream_);
-            t.fwd[0].stat_sums = T.sums.as<double>();
+            k::fill_zero((void*)sums, sizeof(double) * 2 * g.cout, fs);
+            t.fwd[0].stat_sums = sums;
             t.fwd[0].stat_mish = g.has_mish && !g.bn_first;
         }
-        for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, stream_);
-        if (g.out_level >= 0) run_up_resize(plan_, g, T.tw, stream_);
+        for (const ConvLaunch& L : t.fwd) tc::launch_conv(L, fs);
+        if (g.out_level >= 0) run_up_resize(plan_, g, T.tw, fs);
         if (fused_stats) t.fwd[0].stat_sums = nullptr;   // (the launch took its copy)
         if (g.dlib_bn >= 0) {
             const int mish_first = g.bn_first ? 0 : 1;
             float* stats = t_stats_.as<float>() + stats_off_[gi];
             float* rmean = running_.as<float>() + running_off_[gi];
             const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
-            if (!fused_stats) tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, T.sums.as<double>(), stream_, down);
+            if (!fused_stats) tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, sums, fs, down);
             const double m = (double)((long long)n * geo.H * geo.W);
             const float eps = (float)model_.layers[g.dlib_bn].eps;
             if (g.dead) {
-                k::bn_finalize(T.sums.as<double>(), g.cout, (long long)m, eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean, rmean + g.cout, stats,
-                               stream_);
+                k::bn_finalize(sums, g.cout, (long long)m, eps, nu_dev_.as<unsigned long long>() + gi, window_[gi], rmean, rmean + g.cout, stats,
+                               fs);
             } else {
                 // bn_finalize folded into the apply kernel: one launch less per layer
                 tc::BnFinalize fin;
-                fin.sums = T.sums.as<double>(); fin.m = m; fin.eps = (double)eps;
+                fin.sums = sums; fin.m = m; fin.eps = (double)eps;
                 fin.num_updates = nu_dev_.as<unsigned long long>() + gi; fin.window = window_[gi];
                 fin.rmean = rmean; fin.rvar = rmean + g.cout; fin.stats_out = stats;
                 const View y{T.tw.level[g.out_level].as<h16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout, T.tw.level_lo[g.out_level]};
-                tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, stream_, &fin);
+                tc::bn_apply_nhwc(z, y, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, fs, &fin);
             }
         }
     }
+    join_side();
     stats_valid_ = true;
 
     // ---- loss + gradient at the logits (fp32 planes), then h16 [positions][8] for the tensor-core backward
@@ -458,6 +488,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
     static const int nbuckets = getenv("AB_BUCKETS") ? std::max(1, atoi(getenv("AB_BUCKETS"))) : 2;
     // eager: all-reduce the bucket now;  capturing: the bucket ends a graph segment (tc_train_step issues the all-reduce at replay)
     auto bucket_ready = [&](size_t lo, size_t hi) {
+        join_side();   // the bucket's filter gradients are complete
         if (!capture) { allreduce_range(lo, hi); return; }
         if (world_ <= 1 || hi <= lo) return;
         tc_close_segment();
@@ -493,11 +524,14 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
                 tc::channel_sum_nhwc(dzv, geo, T.bias_tmp.as<float>(), stream_, unscale);
                 AB_CUDA(cudaMemcpyAsync(G + g.b_off, T.bias_tmp.p, sizeof(float) * g.cout, cudaMemcpyDeviceToDevice, stream_));
             }
-            if (up) {
-                const View xin{T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
-                tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<h16>() + t.upx_off, geo, stream_);
+            {   // the filter gradient is needed by the optimizer only: off the chain, onto the side stream
+                cudaStream_t ws = fork_side();
+                if (up) {
+                    const View xin{T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
+                    tc::upsample_zero_nhwc(xin, T.tw.geo[g.in_level], T.upx.as<h16>() + t.upx_off, geo, ws);
+                }
+                tc::launch_wgrad_tc(t.wgrad_tc, ws);
             }
-            tc::launch_wgrad_tc(t.wgrad_tc, stream_);
             for (const ConvLaunch& L : t.dgrad) tc::launch_conv(L, stream_);
             if (g.pool_input) {
                 const View gin{T.tg.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin};
@@ -518,6 +552,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         }
         k::slot_to_loss(G + np, t_loss_.as<double>(), world_, stream_);   // mean of the ranks' losses (trainer.h:1206-1253)
     }
+    join_side();
     if (update) optimizer_step();
     AB_CUDA(cudaMemcpyAsync(loss_host_, t_loss_.p, sizeof(double), cudaMemcpyDeviceToHost, stream_));
     AB_CUDA(cudaGetLastError());

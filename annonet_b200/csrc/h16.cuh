@@ -17,6 +17,9 @@ __device__ __forceinline__ void split_half2(float a, float b, __half2& hi, __hal
     hi = sat_half2(a, b);
     const float2 h = __half22float2(hi);
     lo = __floats2half2_rn(a - h.x, b - h.y);
+#ifdef AB_ZERO_LO   // timing experiment only: are fp16 subnormals (the lo halves are ~2^-11 of the value) slow in the tensor pipe?
+    lo = __floats2half2_rn(0.f, 0.f);
+#endif
 }
 
 }  // namespace tc

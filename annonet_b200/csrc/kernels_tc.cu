@@ -123,7 +123,11 @@ __device__ __forceinline__ float mish_fast(float x)
 // Persistent, warp-specialised: one CTA per SM walks work items (a group of `th` M tiles x one N block) with a
 // shared-memory stage ring (TMA -> MMA) and two TMEM accumulator buffers (MMA -> epilogue), so the TMA loads, the
 // tensor-core work and the epilogue of consecutive items overlap.
-template <int NTAPS>
+// KS: K steps (of 16 channels) per chunk, compile-time (kc / 16) so that the MMA issue loop of a tile is straight-line code --
+// one thread issues every tcgen05.mma of the CTA, and with run-time trip counts it spent ~140 cycles per MMA on branches and
+// vector-to-uniform register moves against the ~40 the tensor pipe needs (ncu source view: 80 % of the issuer warp's samples
+// inside the issue loop).  KS = 0: run-time K steps (the rare tap counts).
+template <int NTAPS, int KS>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ ConvLaunch L, const int rev)
 {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -173,9 +177,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 for (int ch = 0; ch < L.nchunks; ++ch, ++it) {
                     const int s = it % L.stages;
                     mbar_wait(&empty_bar[s], ((it / L.stages) & 1) ^ 1);
+                    if (L.dbg & 2) {   // timing experiment (AB_TC_DBG): no loads, the stage is handed over empty
+                        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full_bar[s])) : "memory");
+                        continue;
+                    }
                     mbar_expect(&full_bar[s], tx);
                     const uint32_t a_s = smem0 + (uint32_t)s * L.stage_bytes, b_s = a_s + L.a_stage_bytes;
-                    // split operands: part 0 = A_hi W_hi, 1 = A_lo W_hi, 2 = A_hi W_lo (tc.h)
+                    // split operands: part 0 = the hi halves of A, part 1 = the lo halves, both against the same [W_hi | W_lo] (tc.h)
                     const int part = ch / L.nch1, c1 = ch - part * L.nch1;
                     const int c = L.a_c0 + c1 * L.kc;
                     const int arow = o0 + (part == 1 ? (int)L.a_lo_rows : 0);
@@ -183,7 +191,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         for (int l = 0; l < L.nloads; ++l)
                             tma_2d(a_s + (uint32_t)(sg * L.seg_alloc + l * L.box_rows) * pitch, &L.tmA, c,
                                    arow + L.seg_pos[sg] + l * L.box_rows, &full_bar[s]);
-                    const int bk = part * L.kpart + c1 * L.kc;
+                    const int bk = c1 * L.kc;
 #pragma unroll
                     for (int t = 0; t < NTAPS; ++t)
                         tma_2d(b_s + (uint32_t)(t * L.nblk) * pitch, &L.tmB, bk, t * L.npad_total + n0, &full_bar[s]);
@@ -196,7 +204,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
             const uint32_t idesc = (1u << 4) | ((uint32_t)(L.nblk >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t desc_hi = (uint32_t)(smem_desc_hi(pitch) >> 32);
             const uint32_t lbo = 1u << 16;
-            const int ksteps = L.kc / 16, th = L.th, nblk = L.nblk, nchunks = L.nchunks, stages = L.stages;
+            const int ksteps = KS ? KS : L.kc / 16, th = L.th, nblk = L.nblk, nchunks = L.nchunks, stages = L.stages;
             uint32_t tap_a[NTAPS], tap_b[NTAPS];
 #pragma unroll
             for (int t = 0; t < NTAPS; ++t) {
@@ -218,7 +226,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                     mbar_wait(&full_bar[s], (it / stages) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t a0 = ((smem0 >> 4) + (uint32_t)s * stage16) | lbo, b0 = a0 + b_off16;
-                    if (NTAPS == 9 && kym) {
+                    if (L.dbg & 1) {   // timing experiment (AB_TC_DBG): no MMAs
+                    } else if (NTAPS == 9 && kym) {
                         // input row segment sg feeds output rows sg - u (u = dy + 1) of this item: u in [ulo, uhi]
                         for (int sg = 0; sg < th + 2; ++sg) {
                             const int ulo = max(0, sg - (th - 1)), uhi = min(2, sg);
@@ -226,19 +235,24 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                             const uint32_t idesc_n = (idesc & ~(0x3fu << 17)) | ((nn >> 3) << 17);
                             const uint32_t d = tm + (uint32_t)((sg * 3 + ulo) * nblk);
                             const uint32_t as = a0 + (uint32_t)sg * m_step;
+                            const uint32_t bs = b0 + (uint32_t)ulo * nb16;
 #pragma unroll
                             for (int dxi = 0; dxi < 3; ++dxi)
-                                for (int k = 0; k < ksteps; ++k)
-                                    umma_bf16(d, as + dxi * row16 + 2 * k, b0 + (uint32_t)(dxi * 3 + ulo) * nb16 + 2 * k, desc_hi, idesc_n,
-                                              (uint32_t)(ch | dxi | k));
+#pragma unroll
+                                for (int k = 0; k < (KS ? KS : 4); ++k)
+                                    if (KS || k < ksteps)
+                                        umma_bf16(d, as + dxi * row16 + 2 * k, bs + (uint32_t)(dxi * 3) * nb16 + 2 * k, desc_hi, idesc_n,
+                                                  (dxi | k) ? 1u : (uint32_t)ch);
                         }
                     } else {
                         for (int m = 0; m < th; ++m) {
                             const uint32_t am = a0 + (uint32_t)m * m_step, d = tm + (uint32_t)(m * nblk);
 #pragma unroll
                             for (int t = 0; t < NTAPS; ++t)
-                                for (int k = 0; k < ksteps; ++k)
-                                    umma_bf16(d, am + tap_a[t] + 2 * k, b0 + tap_b[t] + 2 * k, desc_hi, idesc, (uint32_t)(ch | t | k));
+#pragma unroll
+                                for (int k = 0; k < (KS ? KS : 4); ++k)
+                                    if (KS || k < ksteps)
+                                        umma_bf16(d, am + tap_a[t] + 2 * k, b0 + tap_b[t] + 2 * k, desc_hi, idesc, (t | k) ? 1u : (uint32_t)ch);
                         }
                     }
                     umma_commit(&empty_bar[s]);
@@ -285,7 +299,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t tm = tmem + buf * (uint32_t)L.cols_buf + ((uint32_t)(q * 32) << 16);
             // an odd tile count leaves one tile over: the two warp sets split its 16-channel blocks (even / odd)
-            const bool share = (L.th & 1) && nblk >= 32;
+            // split operands: the tile's columns are nsum groups of nout (filters hi | lo) that the epilogue adds
+            const int nsum = L.nsum, nout = nblk / nsum, sstride = L.nsum_stride;
+            const bool share = (L.th & 1) && nout >= 32;
             for (int m = half;; m += kTileStep) {
                 int jpar = -1;
                 if (m >= L.th) {
@@ -315,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                 const bool valid_p = __shfl_xor_sync(0xffffffffu, (int)valid, 1) != 0;
                 const long long posA = odd ? opos_p : opos, posB = odd ? opos : opos_p;
                 const bool okA = odd ? valid_p : valid, okB = odd ? valid : valid_p;
-                for (int j = jpar > 0 ? 16 : 0; j < nblk; j += jpar >= 0 ? 32 : 16) {
+                for (int j = jpar > 0 ? 16 : 0; j < nout; j += jpar >= 0 ? 32 : 16) {
                     float v[16];
                     if (NTAPS == 9 && L.kym) {
                         float w0[16], w1[16];
@@ -326,13 +342,32 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         tmem_ld_fence(v); tmem_ld_fence(w0); tmem_ld_fence(w1);
 #pragma unroll
                         for (int i = 0; i < 16; ++i) v[i] += w0[i] + w1[i];
+                        if (nsum == 2) {
+                            float x0[16];
+                            tmem_ld16_issue(tm + (uint32_t)((m * 3 + 0) * nblk + sstride + j), x0);
+                            tmem_ld16_issue(tm + (uint32_t)(((m + 1) * 3 + 1) * nblk + sstride + j), w0);
+                            tmem_ld16_issue(tm + (uint32_t)(((m + 2) * 3 + 2) * nblk + sstride + j), w1);
+                            tmem_ld_wait();
+                            tmem_ld_fence(x0); tmem_ld_fence(w0); tmem_ld_fence(w1);
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] += (x0[i] + w0[i]) + w1[i];
+                        }
                     } else {
                         tmem_ld16_issue(tm + (uint32_t)(m * nblk + j), v);
-                        tmem_ld_wait();
-                        tmem_ld_fence(v);
+                        if (nsum == 2) {
+                            float x0[16];
+                            tmem_ld16_issue(tm + (uint32_t)(m * nblk + sstride + j), x0);
+                            tmem_ld_wait();
+                            tmem_ld_fence(v); tmem_ld_fence(x0);
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] += x0[i];
+                        } else {
+                            tmem_ld_wait();
+                            tmem_ld_fence(v);
+                        }
                     }
                     const int co0 = n0 + j;
-                    if (co0 >= L.cout) continue;   // (uniform) padding columns only
+                    if (co0 >= L.cout || (L.dbg & 4)) continue;   // (uniform) padding columns only; AB_TC_DBG & 4: no stores
 #pragma unroll
                     for (int i4 = 0; i4 < 4; ++i4) {
                         const float4 b = *reinterpret_cast<const float4*>(&s_bias[co0 + 4 * i4]);
@@ -536,15 +571,19 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
 {
     if (s.cin % 8 || s.src_ctot % 8 || s.a_c0 % 8)
         throw std::invalid_argument("the tensor-core path needs channel counts that are multiples of 8");
-    const int parts = s.split ? 3 : 1;
+    const int parts = s.split ? 2 : 1;
     L.a_c0 = s.a_c0;
     L.ntaps = s.ntaps;
-    L.npad_total = s.npad_total;
+    // split operands: the hi and the lo filters sit side by side along N (tc.h): the GEMM's N doubles, the epilogue adds the halves
+    const int npad_total = s.npad_total * parts;
+    L.npad_total = npad_total;
+    L.nsum = parts; L.nsum_stride = s.npad_total;
     // N block: whole N when it fits one MMA (<= 256), else the smallest even split
-    int nblocks = (s.npad_total + 255) / 256;
-    L.nblk = ((s.npad_total + nblocks - 1) / nblocks + 15) / 16 * 16;
-    nblocks = (s.npad_total + L.nblk - 1) / L.nblk;
-    if (nblocks * L.nblk != s.npad_total) throw std::logic_error("N blocks must tile the padded N");
+    int nblocks = (npad_total + 255) / 256;
+    L.nblk = ((npad_total + nblocks - 1) / nblocks + 15) / 16 * 16;
+    nblocks = (npad_total + L.nblk - 1) / L.nblk;
+    if (nblocks * L.nblk != npad_total) throw std::logic_error("N blocks must tile the padded N");
+    if (s.split && nblocks != 1) throw std::invalid_argument("split operands need the doubled N to fit one MMA (at most 128 output channels)");
     if (s.grid.positions() * (s.split ? 2 : 1) + 4096 >= (1ll << 31))
         throw std::invalid_argument("tensor too large for the tcgen05 conv kernel (positions must fit 31 bits)");
     const int P = s.grid.P();
@@ -628,7 +667,6 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     L.kc = best.kc;
     L.nch1 = (s.cin + L.kc - 1) / L.kc;
     L.nchunks = L.nch1 * parts;
-    L.kpart = padded_k(s.cin);
     L.a_lo_rows = s.split ? s.src_positions : 0;
     L.rows_mode = best.rows_mode != 0; L.kym = best.rows_mode == 2; L.th = best.th; L.nseg = best.nseg; L.nloads = best.nloads; L.box_rows = best.box_rows;
     L.seg_alloc = best.nloads * best.box_rows;
@@ -657,29 +695,43 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
     // activations: 64-byte L2 promotion -- a narrow channel slice costs 64 B of HBM traffic per position instead of 128 (experiments/tma_bench.cu)
     make_map_2d(&L.tmA, s.src, s.src_positions * (s.split ? 2 : 1), s.src_ctot, L.kc, L.box_rows,
                 L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
-    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * s.npad_total, padded_k(s.cin) * parts, L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * npad_total, padded_k(s.cin), L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
 }
 
-template <int NTAPS>
+template <int NTAPS, int KS>
 static void launch_conv_t(const ConvLaunch& L, cudaStream_t st, int rev)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(conv_tc_kernel<NTAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(conv_tc_kernel<NTAPS, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         attr_set = true;
     }
     const long long items = L.grid_x * (L.npad_total / L.nblk);
-    conv_tc_kernel<NTAPS><<<(unsigned)std::min<long long>(items, k::num_sms()), kThreads, L.smem_bytes, st>>>(L, rev);
+    conv_tc_kernel<NTAPS, KS><<<(unsigned)std::min<long long>(items, k::num_sms()), kThreads, L.smem_bytes, st>>>(L, rev);
 }
 
-void launch_conv(const ConvLaunch& L, cudaStream_t st, int rev)
+template <int NTAPS>
+static void launch_conv_k(const ConvLaunch& L, cudaStream_t st, int rev)
 {
+    switch (L.kc) {
+    case 16: launch_conv_t<NTAPS, 1>(L, st, rev); break;
+    case 32: launch_conv_t<NTAPS, 2>(L, st, rev); break;
+    default: launch_conv_t<NTAPS, 4>(L, st, rev); break;
+    }
+}
+
+void launch_conv(const ConvLaunch& L0, cudaStream_t st, int rev)
+{
+    static const int dbg = getenv("AB_TC_DBG") ? atoi(getenv("AB_TC_DBG")) : 0;   // timing experiments: 1 no MMAs, 2 no TMA loads, 4 no stores
+    ConvLaunch Lc;
+    if (dbg) { Lc = L0; Lc.dbg = dbg; }
+    const ConvLaunch& L = dbg ? Lc : L0;
     k::ProfScope ps(k::F_CONV_TC, L.flops, L.bytes, st);
     switch (L.ntaps) {
-    case 1: launch_conv_t<1>(L, st, rev); break;
-    case 2: launch_conv_t<2>(L, st, rev); break;
-    case 4: launch_conv_t<4>(L, st, rev); break;
-    case 9: launch_conv_t<9>(L, st, rev); break;
+    case 1: launch_conv_k<1>(L, st, rev); break;
+    case 2: launch_conv_t<2, 0>(L, st, rev); break;
+    case 4: launch_conv_t<4, 0>(L, st, rev); break;
+    case 9: launch_conv_k<9>(L, st, rev); break;
     default: throw std::logic_error("unsupported tap count");
     }
     k::count_launch();

@@ -501,19 +501,23 @@ __global__ void __launch_bounds__(256) resize_nhwc_kernel(const h16* __restrict_
 __global__ void __launch_bounds__(256) pack_batched_kernel(const float* __restrict__ arena, h16* __restrict__ packs, const PackJob* __restrict__ jobs)
 {
     const PackJob& j = jobs[blockIdx.y];
-    const int kpt = j.kp * j.parts;   // K extent of a packed row: [hi | hi | lo] when the operands are split
-    const long long total = (long long)j.ntaps * j.npad * kpt;
+    const int rows = j.npad * j.parts;   // N rows per tap: [hi filters | lo filters] when the operands are split
+    const long long total = (long long)j.ntaps * rows * j.kp;
     const float* w = arena + j.w_off;
     h16* packed = packs + j.packed_off;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int kk = (int)(i % kpt);
-        const int part = kk / j.kp, kidx = kk - part * j.kp;
-        const int n = (int)((i / kpt) % j.npad);
-        const int t = (int)(i / ((long long)kpt * j.npad));
+        const int kidx = (int)(i % j.kp);
+        const int rr = (int)((i / j.kp) % rows);
+        const int part = rr / j.npad, n = rr - part * j.npad;
+        const int t = (int)(i / ((long long)j.kp * rows));
         float v = 0.f;
         if (n < j.nreal && kidx < j.kreal) v = w[n * j.sn + kidx * j.sk + j.tapmap[t]];
         const h16 hi = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
-        packed[i] = part == 2 ? __float2half_rn(v - __half2float(hi)) : hi;
+#ifdef AB_ZERO_LO
+        packed[i] = part == 1 ? __float2half_rn(0.f) : hi;
+#else
+        packed[i] = part == 1 ? __float2half_rn(v - __half2float(hi)) : hi;
+#endif
     }
 }
 

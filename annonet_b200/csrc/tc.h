@@ -5,8 +5,9 @@
 // parameter-gradient error of ~100 e at the deepest layers (measured and reproduced on the CPU by
 // experiments/bf16_emulation.py; DESIGN.md "Precision").  bf16 storage (e = 2^-9) leaves those gradients 20-35 % off, fp16
 // storage alone 3-8 %.  The TRAINING forward pass therefore keeps every activation as a PAIR of fp16 values (hi + lo, 22
-// significant bits) and every filter as a pair as well, and the forward convolutions run three MMAs per K chunk
-// (A_hi W_hi + A_lo W_hi + A_hi W_lo) -- the tensor pipe has the headroom, the layers are HBM / epilogue bound.  The
+// significant bits) and every filter as a pair as well.  The forward convolutions then compute (A_hi + A_lo)(W_hi + W_lo) as a
+// GEMM with the filter pair side by side along N ([W_hi | W_lo], N doubled) and the activation pair as two K chunks; the
+// epilogue adds the two column halves -- the tensor pipe has the headroom, the layers are HBM / epilogue bound.  The
 // backward pass (gradients, filter gradients) and inference use single fp16 values; gradients are multiplied by a
 // power-of-two loss scale so that they sit in fp16's normal range.
 //
@@ -58,11 +59,14 @@ struct ConvLaunch {
     alignas(64) CUtensorMap tmB;  // packed filters [tap][npad_total][padded K], box {kc, nblk}
     int a_c0 = 0;                 // first channel of the input slice
     int nchunks = 0, kc = 16;     // K = nchunks * kc channels per tap (filters zero-padded beyond the real Cin)
-    // Split operands (training forward): nchunks = 3 * nch1.  Chunk c of part p reads the A box at channel a_c0 + c*kc, row
-    // offset (p == 1 ? a_lo_rows : 0) -- the lo halves live a_lo_rows positions behind the hi halves in the same allocation --
-    // and the B box at K coordinate p*kpart + c*kc of the pack [W_hi | W_hi | W_lo].  Unsplit: nch1 = nchunks.
-    int nch1 = 0, kpart = 0;
+    // Split operands (training forward): nchunks = 2 * nch1.  Chunk c of part p (0: hi halves, 1: lo halves) reads the A box at
+    // channel a_c0 + c*kc, row offset p * a_lo_rows -- the lo halves live a_lo_rows positions behind the hi halves in the same
+    // allocation -- and the SAME B box (K coordinate c*kc) of the pack whose N rows are [W_hi (nsum_stride rows) | W_lo]: the
+    // accumulator holds (A_hi + A_lo) W_hi in columns [0, nsum_stride) and (A_hi + A_lo) W_lo behind them, the epilogue adds
+    // them.  Unsplit: nch1 = nchunks, nsum = 1.
+    int nch1 = 0;
     long long a_lo_rows = 0;
+    int nsum = 1, nsum_stride = 0;   // column groups of one accumulator tile the epilogue adds; their distance
     int ntaps = 0;
     // Tiling of the positions.  The tensor is a 2-D array of [N*(H+1) rows][P columns]; a CTA owns `th` M tiles of
     // 128 positions: FLAT: consecutive runs (tile m starts at o0 + 128*m), one merged halo segment;
@@ -104,6 +108,7 @@ struct ConvLaunch {
     // stored values (of mish(value) with stat_mish) over the valid positions -- what bn_stats_nhwc would re-read z for
     double* stat_sums = nullptr;
     int stat_mish = 0;
+    int dbg = 0;                  // timing experiments only (AB_TC_DBG): 1 skip the MMAs, 2 skip the TMA loads, 4 skip the stores
     long long grid_x = 0;         // CTAs along the positions
     double flops = 0, bytes = 0;  // algorithmic work (for the profiler)
 };
@@ -115,7 +120,8 @@ struct ConvSetup {
     int ntaps = 0; int tap_dy[9] = {0}, tap_dx[9] = {0};  // tap offset = dy*P + dx on the M grid
     int npad_total = 0;
     Geo grid;                      // geometry the M tiles walk over (the source tensor's)
-    // split operands: src holds 2 * src_positions rows (hi halves, then lo halves) and `packed` three K parts of padded_k(cin)
+    // split operands: src holds 2 * src_positions rows (hi halves, then lo halves) and `packed` has 2 * npad_total rows per tap:
+    // the hi filters, then the lo filters (PackJob::parts = 2)
     int split = 0;
 };
 int padded_k(int cin);             // multiple of 64
@@ -199,7 +205,7 @@ struct PackJob {
     long long sn, sk;
     int nreal, npad, kreal, kp, ntaps;
     int tapmap[9];
-    int parts;                     // 1: [tap][n][kp] of fp16(w);  3: [tap][n][3*kp] = [hi | hi | lo], hi = fp16(w), lo = fp16(w - hi)
+    int parts;                     // 1: [tap][n][kp] of fp16(w);  2: [tap][2*npad][kp]: rows n < npad hi = fp16(w), rows npad + n lo = fp16(w - hi)
 };
 void pack_filters_batched(const float* arena, h16* packs, const PackJob* jobs_dev, int njobs, int max_elems, cudaStream_t st);
 

@@ -16,7 +16,7 @@ struct TcGroup {
     int fwd_tapdy[4][9] = {}, fwd_tapdx[4][9] = {};  // tap offset = dy*P + dx of the M grid
     int nlaunch = 1;
     int npad = 0;
-    size_t train_pack_off[4] = {0, 0, 0, 0};   // training forward: split packs [hi | hi | lo] (3 x the K extent), own buffer
+    size_t train_pack_off[4] = {0, 0, 0, 0};   // training forward: split packs (hi and lo filters along N: 2 x the rows), own buffer
     std::vector<tc::ConvLaunch> infer;   // prepared for the current inference geometry
     // training
     std::vector<tc::ConvLaunch> fwd;     // conv -> z (or destination)
@@ -62,7 +62,7 @@ struct TcState {
     DevBuf dpool;              // per transition_down group: gradient at the pooled tensor              [positions][cin]
     DevBuf upx;                // per `up` group: zero-stuffed input on the fine grid (filter gradient)  [positions][cin]
     DevBuf glogits16;          // loss gradient as h16 [positions][8]
-    DevBuf sums, bias_tmp, wscratch, pack_jobs;
+    DevBuf sums, sums_side, bias_tmp, wscratch, pack_jobs;   // sums_side: batch-statistics scratch of the side stream (dead layers)
     int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
     bool train_ready = false;
     std::vector<char> grad_level_needs_zero;   // per level: some writer accumulates into channels nobody assigned before it

@@ -28,7 +28,8 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-CROP, BATCH, CLASSES = 255, 32, 3
+CROP, BATCH, CLASSES = 255, 32, 3          # BASELINE configs[1]; --workload configs3 switches to 511 / 64 per GPU
+WORKLOAD_TAG = "BASELINE configs[1]"
 INFER_SIZE, INFER_TILE = 1024, 1024
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "annonet_ref")
 FWD_FLOP_PER_PX = 85140.0  # live layers: SURVEY App. B sums to 42,570 MAC per input pixel (the survey's 170,281 double-counted)
@@ -149,6 +150,16 @@ def _ref(*args, timeout=3000):
     return r.stdout
 
 
+def reference_infer(size, tile, reps=1):
+    """annonet_infer() of the reference (unmodified annonet_infer.cpp + NetPimpl.cpp, dlib CPU build) on a size x size image"""
+    with tempfile.TemporaryDirectory() as tmp:
+        cfg, net, anet = (os.path.join(tmp, n) for n in ("cfg.net", "net.dnn", "anet.dnn"))
+        _ref("config", CLASSES, 1.0, 1, cfg)
+        _ref("materialize", cfg, net, 5)
+        _ref("runtime", net, anet)
+        return json.loads(_ref("bench_infer", anet, size, size, tile, reps).strip().splitlines()[-1])
+
+
 def reference_train(sample_crops, steps):
     """StartTraining x steps + sync of the reference (NetPimpl::TrainingNet, dlib CPU backend) on
     `sample_crops` crops of CROP x CROP: a bounded sample of the 32-crop minibatch (per-crop cost is
@@ -175,7 +186,7 @@ def reference_arm(args):
         "impl": "reference", "metric": "train_crops_per_s", "value": v, "unit": "crops/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": 0, "ms_per_step": 1e3 * float(out["seconds"]) / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP}, {CLASSES} classes, weighted per-pixel loss, SGD (BASELINE configs[1])",
+        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP} per GPU, {CLASSES} classes, weighted per-pixel loss, SGD ({WORKLOAD_TAG})",
                    "net": "net_type LEVEL_COUNT=6 full width, 2,279,571 params, random init"},
         "cpu_baseline": {"value": v, "unit": "crops/s", "cores": int(out.get("threads", 1)), "kind": "reference",
                          "sample": f"{steps} step(s) of {sample} crops {CROP}x{CROP} (of the {BATCH}-crop minibatch); dlib CPU build, no BLAS, OpenMP im2col"},
@@ -334,7 +345,21 @@ def own_arm(args):
                             "tflops": f["flops"] / (f["ms"] * 1e-3) / 1e12 if f["flops"] else None,
                             "gbs": f["bytes"] / (f["ms"] * 1e-3) / 1e9} for f in sorted(fam, key=lambda f: -f["ms"])}
 
+    # the constant and the per-launch accounting must describe the same work: forward + backward-data + filter gradients of the
+    # live layers = 3 x FWD_FLOP_PER_PX per pixel, minus the first layer's backward-data (the image needs no gradient) and the
+    # border effects of the strided levels (< 1 %)
+    if precision != ab.AB_PRECISION_FP32 and args.workload != "crops256":
+        fam_flops = sum(f["flops"] for f in fam if f["name"] in ("conv_tc", "wgrad_tc")) / args.steps
+        want = 3 * FWD_FLOP_PER_PX * CROP * CROP * BATCH
+        assert 0.93 * want <= fam_flops <= 1.04 * want, f"kernel families account for {fam_flops:.3e} FLOP per step, the constant says {want:.3e}"
+
     cpu = None
+    if infer is not None and world == 1 and not args.no_cpu and os.access(REF_BIN, os.X_OK):
+        # inference cpu_baseline: the reference's annonet_infer() on a 512 x 512 sample (one tile, run at 575 x 575) -- the per-pixel
+        # cost of the CPU path does not depend on the image size (per-tile im2col + GEMM), the 1024 x 1024 image would take minutes
+        out = reference_infer(512, 1024, 1)
+        infer["cpu_baseline"] = {"value": float(out["mpix_per_s"]), "unit": "Mpix/s", "cores": int(out.get("threads", 1)), "kind": "reference",
+                                 "sample": "annonet_infer() of one 512x512 image (1 tile at 575x575) by oracle/_ref/annonet_ref: dlib CPU build, no BLAS"}
     if world == 1 and not args.no_cpu and os.access(REF_BIN, os.X_OK):
         out = reference_train(2, 1)
         cpu = {"value": float(out["crops_per_s"]), "unit": "crops/s", "cores": int(out.get("threads", 1)), "kind": "reference",
@@ -345,7 +370,7 @@ def own_arm(args):
         "metric": "train_crops_per_s", "value": crops / (ms * 1e-3), "unit": "crops/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if precision == ab.AB_PRECISION_FP32 else "f16", "data": "synthetic",
-        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP} per GPU, {CLASSES} classes, weighted per-pixel loss, SGD (BASELINE configs[1])",
+        "config": {"workload": f"annonet_train step: {BATCH} crops {CROP}x{CROP} per GPU, {CLASSES} classes, weighted per-pixel loss, SGD ({WORKLOAD_TAG})",
                    "net": "net_type LEVEL_COUNT=6 full width, 2,279,571 params, random init", "parallelism": f"dp{world}",
                    "l2": "no flush: each step streams GBs of activations, far beyond the 126 MB L2",
                    "roofline_timing": "second pass of the same K steps with a CUDA event pair around every launch",
@@ -552,7 +577,15 @@ def main():
     ap.add_argument("--no-infer16k", action="store_true", help="skip the sharded 16384^2 tiled inference (BASELINE configs[2])")
     ap.add_argument("--sweep", action="store_true", help="BASELINE configs[4]: bisect the largest 1023x1023 mini-batch that fits the GPU")
     ap.add_argument("--sweep-trial", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--workload", default="configs1", choices=["configs1", "configs3", "crops256"],
+                    help="configs1: 32 crops of 255^2 per GPU (headline); configs3: 64 crops of 511^2 per GPU (BASELINE configs[3]); "
+                         "crops256: 32 literal 256^2 crops (resized top join; gradients stop there as in the reference)")
     args = ap.parse_args()
+    global CROP, BATCH, WORKLOAD_TAG
+    if args.workload == "configs3":
+        CROP, BATCH, WORKLOAD_TAG = 511, 64, "BASELINE configs[3]"
+    elif args.workload == "crops256":
+        CROP, BATCH, WORKLOAD_TAG = 256, 32, "BASELINE configs[1] with literal 256x256 crops: bilinear resize at the top join"
     if args.sweep_trial:
         return sweep_trial(args)
     if args.sweep:

@@ -184,7 +184,8 @@ def test_adam_steps_match_the_oracle_solver(ab, precision):
             g = np.abs(grads[i].reshape(-1))
             solid = g > 1e-3 * g.max()
             d = np.abs(a["params"].reshape(-1) - b["params"].reshape(-1))
-            assert d[solid].max() <= 2e-3 * 0.01 + 1e-6 * np.abs(b["params"]).max(), f"step {step} layer<{i}>"
+            if solid.any():
+                assert d[solid].max() <= 2e-3 * 0.01 + 1e-6 * np.abs(b["params"]).max(), f"step {step} layer<{i}>"
             assert d.max() <= 8 * 0.01, f"step {step} layer<{i}>: an Adam step is bounded by a few learning rates ((1 - b1) / sqrt(1 - b2) = 3.2)"
         # continue from the ENGINE's parameters so that rounding differences do not compound across steps
         for (i, a), (_, b) in zip(mine.param_layers(), onet.param_layers()):
