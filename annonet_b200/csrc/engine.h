@@ -117,9 +117,10 @@ private:
     void allreduce_range(size_t lo, size_t hi);
     k::Slice level_slice(Levels& L, int level, int c0, int C) const;
     // h16 tensor-core path (precision_ == AB_PRECISION_F16)
-    void tc_ensure_infer(int h, int w);
-    void tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w);
-    void tc_run_inference(int h, int w);
+    // n: tiles of equal size run as one batch (the coarse levels of a single tile are a handful of CTAs per launch)
+    void tc_ensure_infer(int n, int h, int w);
+    void tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w, int slot = 0, int n = 1);
+    void tc_run_inference(int n, int h, int w);
     void tc_pack_forward_filters();
     void tc_ensure_train(int n, int h, int w);
     void tc_train_step(const uint8_t* imgs_dev, const void* labels_dev, int n, int h, int w, bool update);

@@ -78,7 +78,7 @@ const float* Engine::forward_device(const uint8_t* img_dev, int h, int w)
     AB_CUDA(cudaSetDevice(device_));
     if (precision_ == 1) {  // AB_PRECISION_F16: tcgen05 path
         tc_input(img_dev, h, w, 0, 0, h, w);
-        tc_run_inference(h, w);
+        tc_run_inference(1, h, w);
         return i_logits_.as<float>();
     }
     ensure_infer_ws(h, w);
@@ -190,26 +190,57 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
         canvas_.reserve((size_t)K * plane * sizeof(float));
         AB_CUDA(cudaMemsetAsync(canvas_.p, 0, (size_t)K * plane * sizeof(float), stream_));
     }
+    struct Job { int ti, left, top, rw, rh; };
+    std::vector<Job> jobs;
     for (int ti = me.t0; ti < me.t1; ++ti) {
         const Tile& t = tiles[ti];
         const int fw = t.full[2] - t.full[0] + 1, fh = t.full[3] - t.full[1] + 1;
         const int cx = t.full[0] + fw / 2, cy = t.full[1] + fh / 2;
         const int rw = recommended_input_dimension(fw, plan_.levels), rh = recommended_input_dimension(fh, plan_.levels);
-        const int left = cx - rw / 2, top = cy - rh / 2;
-        if (precision_ == 1) {
-            tc_input(img_dev, h, w, left, top, rh, rw);
-            tc_run_inference(rh, rw);
-        } else {
-            ensure_infer_ws(rh, rw);
-            k::extract_tile(img_dev, h, w, left, top, i_x_.as<float>(), rh, rw, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
-            run_inference_graph(rh, rw);
-        }
+        jobs.push_back(Job{ti, cx - rw / 2, cy - rh / 2, rw, rh});
+    }
+    auto blend = [&](const Job& j, const float* logits) {
+        const Tile& t = tiles[j.ti];
         k::BlendArgs b;   // canvas coordinates: image rows shifted by the band's first row
-        b.logits = i_logits_.as<float>(); b.K = K; b.th = rh; b.tw = rw;
-        b.canvas = canvas_.as<float>(); b.H = rows; b.W = w; b.left = left; b.top = top - me.f0;
+        b.logits = logits; b.K = K; b.th = j.rh; b.tw = j.rw;
+        b.canvas = canvas_.as<float>(); b.H = rows; b.W = w; b.left = j.left; b.top = j.top - me.f0;
         for (int i = 0; i < 4; ++i) { b.full[i] = t.full[i]; b.unique[i] = t.unique[i]; }
         b.full[1] -= me.f0; b.full[3] -= me.f0; b.unique[1] -= me.f0; b.unique[3] -= me.f0;
         k::blend_tile(b, stream_);
+    };
+    if (precision_ == 1) {
+        // Tensor-core path: tiles of equal size run in batches -- one tile alone leaves the coarse levels of the net with a
+        // handful of CTAs per launch.  Batches are formed in tile order among equal sizes (interior tiles all share one size), so
+        // the workspace geometry changes a few times per image; the blend adds commute up to float rounding at 4-tile corners.
+        static const int max_batch = getenv("AB_INFER_BATCH") ? std::max(1, atoi(getenv("AB_INFER_BATCH"))) : 8;
+        std::vector<char> done(jobs.size(), 0);
+        for (size_t i = 0; i < jobs.size(); ++i) {
+            if (done[i]) continue;
+            std::vector<size_t> same;
+            for (size_t j = i; j < jobs.size(); ++j)
+                if (!done[j] && jobs[j].rw == jobs[i].rw && jobs[j].rh == jobs[i].rh) same.push_back(j);
+            // memory bound of a batch: ~0.5 KB per pixel of workspace
+            const int cap = (int)std::max<long long>(1, std::min<long long>(max_batch, (4ll << 30) / (512ll * jobs[i].rw * jobs[i].rh)));
+            for (size_t s0 = 0; s0 < same.size(); s0 += cap) {
+                const int nb = (int)std::min<size_t>(cap, same.size() - s0);
+                for (int q = 0; q < nb; ++q) {
+                    const Job& j = jobs[same[s0 + q]];
+                    tc_input(img_dev, h, w, j.left, j.top, j.rh, j.rw, q, nb);
+                }
+                tc_run_inference(nb, jobs[i].rh, jobs[i].rw);
+                for (int q = 0; q < nb; ++q) {
+                    blend(jobs[same[s0 + q]], i_logits_.as<float>() + (size_t)q * K * jobs[i].rh * jobs[i].rw);
+                    done[same[s0 + q]] = 1;
+                }
+            }
+        }
+    } else {
+        for (const Job& j : jobs) {
+            ensure_infer_ws(j.rh, j.rw);
+            k::extract_tile(img_dev, h, w, j.left, j.top, i_x_.as<float>(), j.rh, j.rw, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+            run_inference_graph(j.rh, j.rw);
+            blend(j, i_logits_.as<float>());
+        }
     }
     // ---- seams: what my tiles added to rows a neighbour owns goes there, what the neighbours' tiles added to my rows comes here
     if (world_ > 1) {

@@ -205,13 +205,13 @@ void run_up_resize(const Plan& plan, const ConvGroup& g, const TcWorkspace& ws, 
     tc::resize_bilinear_nhwc(ws.up_tmp.as<h16>(), ws.split ? (long long)ug.positions() * g.cout : 0, g.cout, ug, out, ws.geo[ol], td, st);
 }
 
-void Engine::tc_ensure_infer(int h, int w)
+void Engine::tc_ensure_infer(int n, int h, int w)
 {
     tc_pack_forward_filters();
     TcState& T = *tc_;
-    if (T.iw.h == h && T.iw.w == w && T.iw.n == 1) return;
-    ensure_workspace(T.iw, plan_, 1, h, w, true, true, false, stream_);
-    i_logits_.reserve((size_t)plan_.class_count * h * w * sizeof(float));
+    if (T.iw.h == h && T.iw.w == w && T.iw.n == n) return;
+    ensure_workspace(T.iw, plan_, n, h, w, true, true, false, stream_);
+    i_logits_.reserve((size_t)n * plan_.class_count * h * w * sizeof(float));
     const float* P = params_.as<float>();
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {
         const ConvGroup& g = plan_.groups[gi];
@@ -228,14 +228,17 @@ void Engine::tc_ensure_infer(int h, int w)
     }
 }
 
-void Engine::tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w)
+void Engine::tc_input(const uint8_t* img_dev, int IH, int IW, int left, int top, int h, int w, int slot, int n)
 {
-    tc_ensure_infer(h, w);
-    tc::image_to_nhwc(img_dev, IH, IW, left, top, tc_->iw.img.as<h16>(), tc_->iw.geo[0], model_.avg[0], model_.avg[1], model_.avg[2], stream_);
+    tc_ensure_infer(n, h, w);
+    tc::Geo one = tc_->iw.geo[0];   // sample `slot` of the batch: positions slot*S ... (tc.h)
+    one.N = 1;
+    tc::image_to_nhwc(img_dev, IH, IW, left, top, tc_->iw.img.as<h16>() + (size_t)slot * one.S() * 8, one, model_.avg[0], model_.avg[1], model_.avg[2], stream_);
 }
 
-void Engine::tc_run_inference(int h, int w)
+void Engine::tc_run_inference(int n, int h, int w)
 {
+    tc_ensure_infer(n, h, w);
     if (model_.is_training) throw state_error("Forward needs a runtime net (anet_type); convert with GetRuntimeNet / as_runtime");
     TcState& T = *tc_;
     for (size_t gi = 0; gi < plan_.groups.size(); ++gi) {

@@ -28,6 +28,19 @@ __device__ __forceinline__ void split8(const float f[8], BF8& hi, BF8& lo)
     for (int i = 0; i < 4; ++i) split_half2(f[2 * i], f[2 * i + 1], hi.v[i], lo.v[i]);
 }
 
+__device__ __forceinline__ BF8 ld8(const h16* p)   // one 16-byte load (a BF8 struct read is emitted as four 4-byte loads)
+{
+    BF8 r;
+    uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+    asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st8(h16* p, const BF8& v)   // one 16-byte store
+{
+    const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+}
+
 __global__ void __launch_bounds__(256) image_to_nhwc_kernel(const uint8_t* __restrict__ img, int IH, int IW, int left, int top,
                                                             h16* __restrict__ out, int N, int H, int W, float ar, float ag, float ab_,
                                                             long long lo_off)
@@ -49,8 +62,8 @@ __global__ void __launch_bounds__(256) image_to_nhwc_kernel(const uint8_t* __res
     const long long pos = n * S + (long long)(y + 1) * (W + 1) + (x + 1);
     BF8 hi, lo;
     split8(f, hi, lo);
-    *reinterpret_cast<BF8*>(out + pos * 8) = hi;
-    if (lo_off) *reinterpret_cast<BF8*>(out + lo_off + pos * 8) = lo;
+    st8(out + pos * 8, hi);
+    if (lo_off) st8(out + lo_off + pos * 8, lo);
 }
 
 __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const h16* __restrict__ in, int in_ctot, int c0, int C8, int N, int Hi, int Wi,
@@ -76,10 +89,10 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const h16* __restrict
         for (int q = 0; q < 3; ++q) {
             const long long pi = n * Si + (long long)(2 * y + r + 1) * (Wi + 1) + (2 * x + q + 1);
             float f[8];
-            unpack8(*reinterpret_cast<const BF8*>(in + pi * in_ctot + c0 + cg * 8), f);
+            unpack8(ld8(in + pi * in_ctot + c0 + cg * 8), f);
             if (in_lo) {   // split tensor: the value is hi + lo (exact in fp32)
                 float l[8];
-                unpack8(*reinterpret_cast<const BF8*>(in + in_lo + pi * in_ctot + c0 + cg * 8), l);
+                unpack8(ld8(in + in_lo + pi * in_ctot + c0 + cg * 8), l);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) f[k] += l[k];
             }
@@ -90,8 +103,8 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const h16* __restrict
     const long long po = n * So + (long long)(y + 1) * (Wo + 1) + (x + 1);
     BF8 hi, lo;
     split8(m, hi, lo);
-    *reinterpret_cast<BF8*>(out + po * (C8 * 8) + cg * 8) = hi;
-    if (out_lo) *reinterpret_cast<BF8*>(out + out_lo + po * (C8 * 8) + cg * 8) = lo;
+    st8(out + po * (C8 * 8) + cg * 8, hi);
+    if (out_lo) st8(out + out_lo + po * (C8 * 8) + cg * 8, lo);
     if (arg) {   // training: which window element won, one byte per channel, for the gradient routing
         uint2 w;
         w.x = a[0] | (a[1] << 8) | (a[2] << 16) | (a[3] << 24);

@@ -50,7 +50,12 @@ __device__ __forceinline__ void ldf8(const float* p, float f[8])
     const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
     f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
 }
-__device__ __forceinline__ void st8(h16* p, const BF8& v) { *reinterpret_cast<BF8*>(p) = v; }
+// one 16-byte store (a struct copy of BF8 is emitted member by member: four 4-byte stores -- seen in the SASS of bn_apply)
+__device__ __forceinline__ void st8(h16* p, const BF8& v)
+{
+    const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+}
 
 struct GeoD { int N, H, W, P; unsigned S; long long total; };  // total = N * S  (< 2^31: checked by geod)
 GeoD geod(const Geo& g)
@@ -478,10 +483,10 @@ __global__ void __launch_bounds__(256) resize_nhwc_kernel(const h16* __restrict_
     const float wtl = __fmul_rn(t.itb[y], t.ilr[x]), wtr = __fmul_rn(t.itb[y], t.lr[x]), wbl = __fmul_rn(t.tb[y], t.ilr[x]), wbr = __fmul_rn(t.tb[y], t.lr[x]);
     auto load = [&](int yy, int xx, float f[8]) {
         const long long e = (n * Si + (long long)(yy + 1) * (iw + 1) + (xx + 1)) * (C8 * 8) + cg * 8;
-        unpack8(*reinterpret_cast<const BF8*>(in + e), f);
+        unpack8(ld8(in + e), f);
         if (in_lo) {
             float l[8];
-            unpack8(*reinterpret_cast<const BF8*>(in + in_lo + e), l);
+            unpack8(ld8(in + in_lo + e), l);
 #pragma unroll
             for (int k = 0; k < 8; ++k) f[k] += l[k];
         }
