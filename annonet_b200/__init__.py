@@ -57,7 +57,7 @@ EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
-    "ab_set_detection_levels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
+    "ab_set_detection_levels", "ab_evaluate_labels", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
@@ -255,6 +255,25 @@ class RuntimeNet(_Net):
         _check(lib.ab_infer_tiled(self._h, _ptr(image), h, w, max_tile_w, max_tile_h, _ptr(g) if g is not None else None, ng,
                                   _ptr(labels), _ptr(blended) if blended is not None else None))
         return (labels, blended) if return_blended else labels
+
+    def evaluate_labels(self, truth: np.ndarray, predicted: np.ndarray, class_count: int):
+        """confusion matrices of annonet_infer_main.cpp (per pixel :482-489, per region :202-272) -> two [K, K] uint64 arrays"""
+        truth = np.ascontiguousarray(truth, dtype=np.uint16)
+        predicted = np.ascontiguousarray(predicted, dtype=np.uint16)
+        h, w = truth.shape
+        assert predicted.shape == (h, w)
+        pp = np.zeros((class_count, class_count), np.uint64)
+        pr = np.zeros((class_count, class_count), np.uint64)
+        _check(lib.ab_evaluate_labels(self._h, _ptr(truth), _ptr(predicted), h, w, class_count, _ptr(pp), _ptr(pr)))
+        return pp, pr
+
+    def render_labels(self, labels: np.ndarray, out_h: int, out_w: int, palette_rgba) -> np.ndarray:
+        """resize_label_image + index_label_image_to_rgba_label_image (annonet_infer_main.cpp:408-418) -> rgba8 [out_h, out_w, 4]"""
+        labels = np.ascontiguousarray(labels, dtype=np.uint16)
+        pal = np.ascontiguousarray(palette_rgba, dtype=np.uint8).reshape(-1, 4)
+        out = np.empty((out_h, out_w, 4), np.uint8)
+        _check(lib.ab_render_labels(self._h, _ptr(labels), labels.shape[0], labels.shape[1], out_h, out_w, _ptr(pal), pal.shape[0], _ptr(out)))
+        return out
 
     def set_detection_levels(self, levels: Optional[Sequence[float]]) -> None:
         """annonet_infer()'s detection_levels (annonet_infer.cpp:187-239); None / empty switches the blob filter off"""

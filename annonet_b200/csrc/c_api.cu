@@ -173,6 +173,25 @@ ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, in
     return guarded([&] { E(net).infer_tiled_host(image_hwc, h, w, max_tile_w, max_tile_h, gains, ngains, labels_host, blended_host); });
 }
 
+ab_status ab_evaluate_labels(ab_net* net, const uint16_t* truth, const uint16_t* predicted, int h, int w, int class_count, uint64_t* per_pixel,
+                             uint64_t* per_region)
+{
+    return guarded([&] {
+        if (!truth || !predicted || !per_pixel || h < 1 || w < 1) throw std::invalid_argument("bad arguments");
+        static_assert(sizeof(uint64_t) == sizeof(unsigned long long), "64-bit counters");
+        E(net).evaluate_labels(truth, predicted, h, w, class_count, (unsigned long long*)per_pixel, (unsigned long long*)per_region);
+    });
+}
+
+ab_status ab_render_labels(ab_net* net, const uint16_t* labels, int h, int w, int out_h, int out_w, const uint8_t* palette_rgba, int class_count,
+                           uint8_t* rgba_out)
+{
+    return guarded([&] {
+        if (!labels || !palette_rgba || !rgba_out) throw std::invalid_argument("bad arguments");
+        E(net).render_labels(labels, h, w, out_h, out_w, palette_rgba, class_count, rgba_out);
+    });
+}
+
 ab_status ab_set_detection_levels(ab_net* net, const double* levels, int n)
 {
     return guarded([&] {

@@ -82,6 +82,10 @@ public:
     // seams are exchanged with the neighbours and every rank ends up with the whole label map (engine_infer.cu)
     void infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                             uint16_t* labels_dev);
+    // annonet_infer_main.cpp's evaluation (confusion matrices :482-491, per region :202-272) and result image (:408-418); host buffers
+    void evaluate_labels(const uint16_t* truth, const uint16_t* predicted, int h, int w, int K, unsigned long long* per_pixel,
+                         unsigned long long* per_region);
+    void render_labels(const uint16_t* labels, int h, int w, int out_h, int out_w, const uint8_t* palette_rgba, int K, uint8_t* rgba_out);
     void set_detection_levels(const double* levels, int n) { detection_levels_.assign(levels, levels + (levels ? n : 0)); }
     void infer_tiled_host(const uint8_t* img_host, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                           uint16_t* labels_host, float* blended_host);
@@ -150,6 +154,7 @@ private:
 
     // inference workspace
     Levels iw_;
+    DevBuf e_truth_, e_pred_, e_roots_, e_counts_, e_rgba_;   // evaluation / write-back scratch
     DevBuf i_up_, t_up_;   // the up-sampled tensor of a join that needs the bilinear resize (non-canonical input sizes)
     DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_, det_dev_, seeds_, blob_parent_, blob_keep_;
     std::vector<double> detection_levels_;   // annonet_infer()'s detection_levels; empty or all zero: no blob filter

@@ -319,6 +319,77 @@ void Engine::infer_tiled_device(const uint8_t* img_dev, int h, int w, int max_ti
     AB_CUDA(cudaGetLastError());
 }
 
+// confusion_matrix_per_pixel (annonet_infer_main.cpp:482-489) on the device; update_confusion_matrix_per_region (:202-272) with
+// the connected blobs of both label images found on the device (union-find, kernels_blobs.cu) and the per-blob class votes
+// counted on the host from the blob ids -- one linear pass, the expensive part of the reference (two flood fills) is gone.
+void Engine::evaluate_labels(const uint16_t* truth, const uint16_t* predicted, int h, int w, int K, unsigned long long* per_pixel,
+                             unsigned long long* per_region)
+{
+    AB_CUDA(cudaSetDevice(device_));
+    if (K < 1 || K > 64) throw std::invalid_argument("evaluate_labels: 1..64 classes");
+    const size_t n = (size_t)h * w;
+    e_truth_.reserve(n * 2); e_pred_.reserve(n * 2); e_roots_.reserve(n * 4); blob_keep_.reserve(n); e_counts_.reserve(sizeof(unsigned long long) * K * K);
+    AB_CUDA(cudaMemcpyAsync(e_truth_.p, truth, n * 2, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaMemcpyAsync(e_pred_.p, predicted, n * 2, cudaMemcpyHostToDevice, stream_));
+    k::confusion_per_pixel(e_truth_.as<uint16_t>(), e_pred_.as<uint16_t>(), (long long)n, K, e_counts_.as<unsigned long long>(), stream_);
+    AB_CUDA(cudaMemcpyAsync(per_pixel, e_counts_.p, sizeof(unsigned long long) * K * K, cudaMemcpyDeviceToHost, stream_));
+    if (!per_region) { synchronize(); return; }
+    std::fill(per_region, per_region + (size_t)K * K, 0ull);
+    bool any_labelled = false;
+    for (size_t i = 0; i < n && !any_labelled; ++i) any_labelled = truth[i] != 65535;
+    if (!any_labelled) { synchronize(); return; }   // labeled_points_by_class.empty() (:210-212)
+    std::vector<int> roots(n);
+    const uint16_t ignore = 65535;
+    for (int pass = 0; pass < 2; ++pass) {   // blobs of the ground truth, then of the result (:269-270)
+        k::label_blobs((pass == 0 ? e_truth_ : e_pred_).as<uint16_t>(), h, w, e_roots_.as<int>(), blob_keep_.as<uint8_t>(), stream_);
+        AB_CUDA(cudaMemcpyAsync(roots.data(), e_roots_.p, n * 4, cudaMemcpyDeviceToHost, stream_));
+        synchronize();
+        // blob numbers: background (-1) is blob 0 like dlib's, every other blob gets the next free number
+        std::vector<int> number(n, -1);
+        int blobs = 1;
+        std::vector<unsigned> votes_gt(K), votes_pred(K);   // grown below: [blob][class]
+        for (size_t i = 0; i < n; ++i)
+            if (roots[i] >= 0 && number[roots[i]] < 0) number[roots[i]] = blobs++;
+        votes_gt.assign((size_t)blobs * K, 0); votes_pred.assign((size_t)blobs * K, 0);
+        std::vector<unsigned> pred_other((size_t)blobs, 0);   // votes for predictions outside [0, K)
+        for (size_t i = 0; i < n; ++i) {
+            if (truth[i] == ignore) continue;          // not a labelled point
+            const int b = roots[i] < 0 ? 0 : number[roots[i]];
+            if (truth[i] < K) ++votes_gt[(size_t)b * K + truth[i]];
+            if (predicted[i] < K) ++votes_pred[(size_t)b * K + predicted[i]]; else ++pred_other[b];
+        }
+        auto winner = [&](const unsigned* v, int from) -> int {   // most votes, lowest class among ties; -1: no votes at all
+            int best = -1; unsigned most = 0;
+            for (int c = from; c < K; ++c) if (v[c] > most) { most = v[c]; best = c; }
+            return best;
+        };
+        for (int b = 0; b < blobs; ++b) {
+            const unsigned* gt = &votes_gt[(size_t)b * K];
+            unsigned* pr = &votes_pred[(size_t)b * K];
+            const int wgt = winner(gt, 0);
+            if (wgt < 0) continue;                                       // winner == label_to_ignore: no labelled point in the blob
+            bool only_background = pr[0] > 0 && pred_other[b] == 0;
+            for (int c = 1; c < K && only_background; ++c) only_background = pr[c] == 0;
+            if (wgt != 0 && !only_background) pr[0] = 0;                 // detections count, however small (:249-256)
+            const int wpr = winner(pr, 0);
+            if (wpr >= 0) ++per_region[(size_t)wgt * K + wpr];
+        }
+    }
+}
+
+void Engine::render_labels(const uint16_t* labels, int h, int w, int out_h, int out_w, const uint8_t* palette_rgba, int K, uint8_t* rgba_out)
+{
+    AB_CUDA(cudaSetDevice(device_));
+    if (h < 1 || w < 1 || out_h < 1 || out_w < 1 || K < 1) throw std::invalid_argument("render_labels: bad size");
+    const size_t n = (size_t)h * w, on = (size_t)out_h * out_w;
+    e_pred_.reserve(n * 2); e_rgba_.reserve(on * 4); e_counts_.reserve(std::max<size_t>((size_t)K * 4, 64 * 64 * 8));
+    AB_CUDA(cudaMemcpyAsync(e_pred_.p, labels, n * 2, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaMemcpyAsync(e_counts_.p, palette_rgba, (size_t)K * 4, cudaMemcpyHostToDevice, stream_));
+    k::render_labels(e_pred_.as<uint16_t>(), h, w, out_h, out_w, e_counts_.as<uint8_t>(), K, e_rgba_.as<uint8_t>(), stream_);
+    AB_CUDA(cudaMemcpyAsync(rgba_out, e_rgba_.p, on * 4, cudaMemcpyDeviceToHost, stream_));
+    synchronize();
+}
+
 void Engine::infer_tiled_host(const uint8_t* img_host, int h, int w, int max_tile_w, int max_tile_h, const double* gains, int ngains,
                               uint16_t* labels_host, float* blended_host)
 {

@@ -102,6 +102,13 @@ void argmax_labels(const float* planes, long long plane_stride, int K, long long
 // annonet_infer.cpp:214-239: blobs of equal non-zero labels (8-neighbourhood) without a seed are set to 0.
 // parent: h*w ints, keep: h*w bytes of scratch.  transposed_seeds: mirror the reference's (r, c) -> point(x = r, y = c) ->
 // blobs(y, x) seed lookup (annonet_infer.cpp:210,221) instead of the evidently intended same-pixel lookup.
+// ---- evaluation and write-back of annonet_infer_main.cpp (confusion matrices :91-272,482-491; result images :408-418) --------
+// connected blobs of equal non-zero labels (8-neighbourhood): roots[i] = -1 (background) or the blob's smallest pixel index
+void label_blobs(const uint16_t* labels, int h, int w, int* roots, uint8_t* scratch_bytes, cudaStream_t st);
+// counts[t * K + p] = number of pixels with truth t < K and prediction p < K (ignored truth 65535 drops out)
+void confusion_per_pixel(const uint16_t* truth, const uint16_t* pred, long long n, int K, unsigned long long* counts, cudaStream_t st);
+// nearest-neighbour resize of a label map to oh x ow (dlib's rounding) + class colours -> rgba8
+void render_labels(const uint16_t* labels, int ih, int iw, int oh, int ow, const uint8_t* palette_rgba, int K, uint8_t* out_rgba, cudaStream_t st);
 void filter_detections(uint16_t* labels, const uint8_t* seeds, int h, int w, int* parent, uint8_t* keep, cudaStream_t st, int transposed_seeds = 1);
 // blend (annonet_infer.cpp:102-164): canvas[k, Y, X] (+)= t * logits[k, y, x]
 struct BlendArgs {

@@ -137,6 +137,17 @@ ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, in
  * rank's rows only, zero elsewhere.) */
 ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, int max_tile_w, int max_tile_h,
                          const double* gains, int ngains, uint16_t* labels_host, float* blended_host);
+/* Evaluation of annonet_infer_main.cpp: confusion_matrix_per_pixel (:482-489) and update_confusion_matrix_per_region
+ * (:202-272: connected blobs of the ground truth and of the result, one vote per labelled pixel, a non-background region's
+ * prediction is background only if nothing else was predicted in it).  truth / predicted: h*w uint16 (host), 65535 = not
+ * labelled.  per_pixel / per_region: class_count^2 counters [truth][predicted]; per_region may be NULL. */
+ab_status ab_evaluate_labels(ab_net* net, const uint16_t* truth, const uint16_t* predicted, int h, int w, int class_count,
+                             uint64_t* per_pixel, uint64_t* per_region);
+/* The result image of annonet_infer_main.cpp:408-418: resize_label_image (nearest neighbour, annonet.cpp:132-141) to
+ * out_h x out_w fused with index_label_image_to_rgba_label_image (:74-86); palette_rgba: class_count x 4 bytes,
+ * rgba_out: out_h*out_w*4 bytes (host; the caller writes the PNG). */
+ab_status ab_render_labels(ab_net* net, const uint16_t* labels, int h, int w, int out_h, int out_w, const uint8_t* palette_rgba,
+                           int class_count, uint8_t* rgba_out);
 /* annonet_infer()'s detection_levels argument (annonet_infer.cpp:32-41,187-239; the CLI's -d option): with any level > 0
  * the label map of every following ab_infer_tiled* call goes through the blob filter -- connected blobs of equal non-zero
  * labels (dlib::label_connected_blobs, 8-neighbourhood) that contain no pixel with

@@ -718,6 +718,68 @@ def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels:
     return out
 
 
+def confusion_per_pixel(truth: np.ndarray, predicted: np.ndarray, k: int) -> np.ndarray:
+    """confusion_matrix_per_pixel, annonet_infer_main.cpp:482-489: [truth][predicted] over the labelled pixels (truth != 65535)."""
+    m = (truth < k) & (predicted < k)
+    out = np.zeros((k, k), dtype=np.uint64)
+    np.add.at(out, (truth[m].astype(np.int64), predicted[m].astype(np.int64)), 1)
+    return out
+
+
+def confusion_per_region(truth: np.ndarray, predicted: np.ndarray, k: int) -> np.ndarray:
+    """update_confusion_matrix_per_region, annonet_infer_main.cpp:202-272: for the connected blobs (equal non-zero labels,
+    8-neighbourhood; all zero pixels together are blob 0) of the ground truth and then of the result, every labelled pixel
+    votes for its truth and its prediction; in a blob whose ground truth is predominantly non-background the background
+    prediction is dropped unless it is the only one; the blob adds one count at [truth winner][prediction winner].
+    (The reference picks the winner with max_element over an unordered_map: ties are iteration-order dependent there, the
+    lowest class here.)"""
+    from scipy import ndimage
+    out = np.zeros((k, k), dtype=np.uint64)
+    labelled = truth != LABEL_TO_IGNORE
+    if not labelled.any():
+        return out
+    for img in (truth, predicted):
+        comp = np.zeros(img.shape, dtype=np.int64)
+        nxt = 1
+        for value in np.unique(img):
+            if value == 0:
+                continue
+            c, n = ndimage.label(img == value, structure=np.ones((3, 3), dtype=bool))
+            comp[c > 0] = c[c > 0] + (nxt - 1)
+            nxt += n
+        vg = np.zeros((nxt, k), dtype=np.int64)
+        vp = np.zeros((nxt, k), dtype=np.int64)
+        b = comp[labelled]
+        np.add.at(vg, (b, truth[labelled].astype(np.int64)), 1)
+        np.add.at(vp, (b, predicted[labelled].astype(np.int64)), 1)
+        for blob in range(nxt):
+            if vg[blob].sum() == 0:
+                continue
+            wgt = int(np.argmax(vg[blob]))
+            only_background = vp[blob, 0] > 0 and vp[blob, 1:].sum() == 0
+            if wgt != 0 and not only_background:
+                vp[blob, 0] = 0
+            out[wgt, int(np.argmax(vp[blob]))] += 1
+    return out
+
+
+def render_labels(labels: np.ndarray, out_h: int, out_w: int, palette_rgba: np.ndarray) -> np.ndarray:
+    """resize_label_image (annonet.cpp:132-141: dlib::resize_image + interpolate_nearest_neighbor, i.e. source pixel
+    floor(c * (iw-1)/max(ow-1,1) + 0.5), image_transforms/interpolation.h:559-593 and dlib's vector<double> -> point rounding)
+    followed by index_label_image_to_rgba_label_image (annonet_infer_main.cpp:74-86)."""
+    ih, iw = labels.shape
+    ys = (ih - 1) / float(max(out_h - 1, 1))
+    xs = (iw - 1) / float(max(out_w - 1, 1))
+    sy = np.floor(np.arange(out_h) * ys + 0.5).astype(np.int64)
+    sx = np.floor(np.arange(out_w) * xs + 0.5).astype(np.int64)
+    idx = labels[sy][:, sx].astype(np.int64)
+    pal = np.asarray(palette_rgba, dtype=np.uint8).reshape(-1, 4)
+    out = np.zeros((out_h, out_w, 4), dtype=np.uint8)
+    ok = idx < pal.shape[0]
+    out[ok] = pal[idx[ok]]
+    return out
+
+
 def set_weights(labels: np.ndarray, class_weight: float, image_weight: float) -> np.ndarray:
     """set_weights, annonet_train.h:20-83.  labels u16 [H,W] -> f32 weights [H,W]."""
     nr, nc = labels.shape

@@ -40,3 +40,45 @@ def write_anno_dataset(directory, rng, count, h, w, synth_image):
         mask[:, w // 2 - 3:w // 2 + 3] = (0, 0, 0, 0)
         write_png(os.path.join(directory, f"{i}.png"), img)
         write_png(os.path.join(directory, f"{i}.png_mask.png"), mask)
+
+
+def read_png(path):
+    """8-bit RGB / RGBA PNG -> array (handles the five scanline filters; enough for dlib's save_png output)"""
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h, ctype = 8, b"", 0, 0, 0
+    while pos < len(data):
+        n, tag = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        if tag == b"IHDR":
+            w, h, depth, ctype = struct.unpack(">IIBB", body[:10])
+            assert depth == 8 and ctype in (2, 6)
+        elif tag == b"IDAT":
+            idat += body
+        pos += 12 + n
+    c = 3 if ctype == 2 else 4
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + w * c)
+    out = np.zeros((h, w * c), np.int32)
+    for y in range(h):
+        f, line = int(raw[y, 0]), raw[y, 1:].astype(np.int32)
+        prev = out[y - 1] if y else np.zeros(w * c, np.int32)
+        if f == 0:
+            out[y] = line
+        elif f == 2:
+            out[y] = (line + prev) & 255
+        else:
+            cur = np.zeros(w * c, np.int32)
+            for x in range(w * c):
+                a = cur[x - c] if x >= c else 0
+                b = prev[x]
+                cc = prev[x - c] if x >= c else 0
+                if f == 1:
+                    p = a
+                elif f == 3:
+                    p = (a + b) // 2
+                else:
+                    pa, pb, pc = abs(b - cc), abs(a - cc), abs(a + b - 2 * cc)
+                    p = a if (pa <= pb and pa <= pc) else (b if pb <= pc else cc)
+                cur[x] = (line[x] + p) & 255
+            out[y] = cur
+    return out.reshape(h, w, c).astype(np.uint8)

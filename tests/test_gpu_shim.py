@@ -117,3 +117,78 @@ def test_trainer_state_file_is_interchangeable_with_the_reference():
                     worst = max(worst, rel_err(db, da))
             print(f"state file {tag}: resumed nets identical; one resumed step moves the parameters alike (max-rel {worst:.2e})")
             assert worst < 2e-2
+
+
+def _label_maps(rng, h, w, k):
+    yy, xx = np.mgrid[0:h, 0:w]
+    truth = ((((yy // 23) + (xx // 31)) % (k + 1))).astype(np.uint16)
+    truth[truth == k] = 0                                          # plenty of background
+    truth[rng.random((h, w)) < 0.03] = 65535                       # unlabelled pixels
+    pred = truth.copy()
+    pred[pred == 65535] = 0
+    flip = rng.random((h, w)) < 0.08
+    pred[flip] = rng.integers(0, k, size=int(flip.sum()), dtype=np.uint16)
+    pred[40:60, 10:90] = 0                                         # a missed region
+    return truth, pred
+
+
+def test_confusion_matrices_and_result_image_match_oracle(ab):
+    """annonet_infer_main.cpp's evaluation: per-pixel and per-region confusion matrices (:202-272,482-491) and the result image
+    (:408-418: nearest-neighbour label upscale + class colours) on the device against the oracle's restatement"""
+    import annonet_numpy as on
+    rng = np.random.default_rng(31)
+    rt = ab.RuntimeNet(0, ab.AB_PRECISION_FP32)
+    for (h, w, k) in ((200, 260, 4), (97, 131, 3), (64, 64, 8)):
+        truth, pred = _label_maps(rng, h, w, k)
+        pp, pr = rt.evaluate_labels(truth, pred, k)
+        assert np.array_equal(pp, on.confusion_per_pixel(truth, pred, k))
+        ref_pr = on.confusion_per_region(truth, pred, k)
+        assert np.array_equal(pr, ref_pr), (pr, ref_pr)
+        assert pr.sum() > 4
+        palette = rng.integers(0, 256, size=(k, 4), dtype=np.uint8)
+        for (oh, ow) in ((h, w), (2 * h + 3, 3 * w - 1), (h // 2 + 1, w // 3 + 2), (1, 1)):
+            assert np.array_equal(rt.render_labels(pred, oh, ow, palette), on.render_labels(pred, oh, ow, palette))
+    unlabelled = np.full((50, 60), 65535, np.uint16)
+    pp, pr = rt.evaluate_labels(unlabelled, np.zeros((50, 60), np.uint16), 3)
+    assert pp.sum() == 0 and pr.sum() == 0
+
+
+INFER_BIN = os.path.join(ROOT, "shim", "_build", "annonet_infer")
+INFER_REF_BIN = os.path.join(ROOT, "shim", "_build", "annonet_infer_reference")
+
+
+@pytest.mark.skipif(not (os.access(INFER_BIN, os.X_OK) and os.access(INFER_REF_BIN, os.X_OK)), reason="shim/_build/annonet_infer* not built")
+def test_reference_infer_cli_over_the_engine_matches_the_reference_cli():
+    """the UNMODIFIED annonet_infer_main.cpp over the engine (shim) and over the reference's own NetPimpl.cpp: same annonet.dnn,
+    same PNG dataset with ground-truth masks, gains and detection levels on the command line -- the result PNGs and the two
+    printed confusion matrices must agree (a handful of near-tie pixels aside)."""
+    import annonet_numpy as on
+    from conftest import ref_random_net
+    from png_util import read_png
+    rng = np.random.default_rng(12)
+    outs = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        w = df.Writer()
+        anet = ref_random_net(3, 5, training=False)
+        w.string(""); w.float(1.0, 53); w.int(len(anet)); w.parts.append(anet)     # annonet_train_main.cpp:557-565
+        for who, exe in (("engine", INFER_BIN), ("reference", INFER_REF_BIN)):
+            d = os.path.join(tmp, who)
+            os.makedirs(os.path.join(d, "data"))
+            open(os.path.join(d, "annonet.dnn"), "wb").write(w.bytes())
+            write_anno_dataset(os.path.join(d, "data"), np.random.default_rng(5), 2, 200, 330, synth_image)
+            out = _run([exe, os.path.join(d, "data"), "-w", 256, "-h", 256, "-g", "1:0.05", "-g", "2:-0.02",
+                        "--full-image-reader-thread-count", 1, "--result-image-writer-thread-count", 1], cwd=d, env={"AB_PRECISION": "1"}, timeout=1500)
+            assert "Confusion matrix per pixel" in out
+            mats = out[out.index("Confusion matrix per pixel"):]
+            pngs = {f: read_png(os.path.join(d, "data", f)) for f in sorted(os.listdir(os.path.join(d, "data"))) if f.endswith("_result.png")}
+            assert len(pngs) == 2
+            outs[who] = (mats, pngs)
+    (m_e, p_e), (m_r, p_r) = outs["engine"], outs["reference"]
+    agree = min(float(np.mean(np.all(p_e[f] == p_r[f], axis=-1))) for f in p_r)
+    print(f"annonet_infer CLI over the engine vs the reference: result PNGs agree on {agree:.5f} of the pixels")
+    print(m_e)
+    assert agree >= 0.999
+    nums = lambda s: [float(t) for t in s.replace("%", " ").split() if t.replace(".", "", 1).isdigit()]
+    ne, nr = nums(m_e), nums(m_r)
+    assert len(ne) == len(nr) and len(ne) > 20
+    assert sum(abs(a - b) for a, b in zip(ne, nr)) <= 0.002 * sum(nr)
