@@ -48,6 +48,12 @@ class _KernelStat(C.Structure):
     _fields_ = [("name", C.c_char * 24), ("launches", C.c_uint64), ("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double)]
 
 
+class Crop(C.Structure):
+    """ab_crop (include/annonet_b200.h): one crop of a device-resident dataset image and its augmentation"""
+    _fields_ = [("image", C.c_int32), ("left", C.c_int32), ("top", C.c_int32), ("flip_lr", C.c_int32), ("flip_ud", C.c_int32),
+                ("brightness", C.c_double), ("noise_level", C.c_int32), ("seed", C.c_uint32), ("color_offset", C.c_int32 * 3)]
+
+
 class _Tile(C.Structure):
     _fields_ = [("full", C.c_int32 * 4), ("non_overlapping", C.c_int32 * 4), ("unique", C.c_int32 * 4)]
 
@@ -57,7 +63,7 @@ EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
-    "ab_set_detection_levels", "ab_evaluate_labels", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
+    "ab_dataset_clear", "ab_dataset_add", "ab_build_crops", "ab_copy_to_host", "ab_train_step_crops", "ab_set_detection_levels", "ab_evaluate_labels", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
@@ -342,6 +348,47 @@ class TrainingNet(_Net):
 
     def train_step_device(self, images_ptr: int, labels_ptr: int, n: int, h: int, w: int) -> None:
         _check(lib.ab_train_step_device(self._h, C.c_void_p(images_ptr), C.c_void_p(labels_ptr), n, h, w))
+
+    # ---- device-resident dataset + mini-batch assembly (annonet_train_main.cpp:110-232 on the GPU)
+    def dataset_clear(self) -> None:
+        _check(lib.ab_dataset_clear(self._h))
+
+    def dataset_add(self, rgb: np.ndarray, labels: np.ndarray) -> int:
+        rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
+        labels = np.ascontiguousarray(labels, dtype=np.uint16)
+        h, w, _ = rgb.shape
+        assert labels.shape == (h, w)
+        idx = C.c_int(0)
+        _check(lib.ab_dataset_add(self._h, _ptr(rgb), _ptr(labels), h, w, C.byref(idx)))
+        return idx.value
+
+    @staticmethod
+    def _crop_array(crops):
+        arr = (Crop * len(crops))()
+        for i, c in enumerate(crops):
+            arr[i].image, arr[i].left, arr[i].top = c["image"], c["left"], c["top"]
+            arr[i].flip_lr, arr[i].flip_ud = int(c.get("flip_lr", 0)), int(c.get("flip_ud", 0))
+            arr[i].brightness, arr[i].noise_level, arr[i].seed = float(c.get("brightness", 1.0)), int(c.get("noise_level", 0)), int(c.get("seed", 0))
+            for q, v in enumerate(c.get("color_offset", (0, 0, 0))):
+                arr[i].color_offset[q] = int(v)
+        return arr
+
+    def build_crops(self, crops, dim: int, class_weight: float, image_weight: float):
+        """the mini-batch as the device wrote it: (u8 [n, dim, dim, 3], WLABEL [n, dim, dim]) copied back for inspection"""
+        arr = self._crop_array(crops)
+        pi, pl = C.c_void_p(), C.c_void_p()
+        _check(lib.ab_build_crops(self._h, arr, len(crops), dim, C.c_double(class_weight), C.c_double(image_weight), C.byref(pi), C.byref(pl)))
+        self.synchronize()
+        n = len(crops)
+        imgs = np.empty((n, dim, dim, 3), np.uint8)
+        labs = np.empty((n, dim, dim), WLABEL)
+        _check(lib.ab_copy_to_host(self._h, _ptr(imgs), pi, C.c_size_t(imgs.nbytes)))
+        _check(lib.ab_copy_to_host(self._h, _ptr(labs), pl, C.c_size_t(labs.nbytes)))
+        return imgs, labs
+
+    def train_step_crops(self, crops, dim: int, class_weight: float, image_weight: float) -> None:
+        arr = self._crop_array(crops)
+        _check(lib.ab_train_step_crops(self._h, arr, len(crops), dim, C.c_double(class_weight), C.c_double(image_weight)))
 
     def sync(self) -> float:
         loss = C.c_double(0)

@@ -343,6 +343,40 @@ ab_status ab_gradient_arena(ab_net* net, void** grads_dev, size_t* count_floats)
     });
 }
 
+ab_status ab_dataset_clear(ab_net* net) { return guarded([&] { E(net).dataset_clear(); }); }
+ab_status ab_dataset_add(ab_net* net, const uint8_t* rgb, const uint16_t* labels, int h, int w, int* index)
+{
+    return guarded([&] { const int i = E(net).dataset_add(rgb, labels, h, w); if (index) *index = i; });
+}
+static_assert(sizeof(ab_crop) == sizeof(ab::Engine::CropSpec), "ab_crop mirrors Engine::CropSpec");
+ab_status ab_build_crops(ab_net* net, const ab_crop* crops, int n, int dim, double class_weight, double image_weight, const void** imgs_dev,
+                         const void** labels_dev)
+{
+    return guarded([&] {
+        const uint8_t* im = nullptr; const void* lb = nullptr;
+        E(net).build_crops((const ab::Engine::CropSpec*)crops, n, dim, class_weight, image_weight, &im, &lb);
+        if (imgs_dev) *imgs_dev = im;
+        if (labels_dev) *labels_dev = lb;
+    });
+}
+ab_status ab_train_step_crops(ab_net* net, const ab_crop* crops, int n, int dim, double class_weight, double image_weight)
+{
+    return guarded([&] {
+        const uint8_t* im = nullptr; const void* lb = nullptr;
+        ab::Engine& e = E(net);
+        e.build_crops((const ab::Engine::CropSpec*)crops, n, dim, class_weight, image_weight, &im, &lb);
+        e.train_step_device(im, lb, n, dim, dim, true);
+    });
+}
+
+ab_status ab_copy_to_host(ab_net* net, void* dst_host, const void* src_dev, size_t bytes)
+{
+    return guarded([&] {
+        E(net).synchronize();
+        if (cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); throw ab::cuda_error("ab_copy_to_host: cudaMemcpy failed"); }
+    });
+}
+
 ab_status ab_comm_unique_id(void* id128) { return guarded([&] { ab::nccl_unique_id(id128); }); }
 ab_status ab_comm_init(ab_net* net, const void* id128, int rank, int world) { return guarded([&] { E(net).comm_init(id128, rank, world); }); }
 

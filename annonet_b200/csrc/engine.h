@@ -105,6 +105,13 @@ public:
     // all tensors of one resolution level after the last training step (activations or their gradients), NCHW fp32
     void level_values(int level, bool gradient, std::vector<float>& out, int dims[4]);
 
+    // ---- device-resident dataset + mini-batch assembly (kernels_crop.cu; annonet_train_main.cpp:110-232,520-553)
+    struct CropSpec { int image, left, top, flip_lr, flip_ud; double brightness; int noise_level; unsigned seed; int color_offset[3]; };
+    void dataset_clear();
+    int dataset_add(const uint8_t* rgb, const uint16_t* labels, int h, int w);
+    // crops + weighted labels into the step's input buffers (returned), ready for train_step_device
+    void build_crops(const CropSpec* crops, int n, int dim, double class_weight, double image_weight, const uint8_t** imgs_dev, const void** labels_dev);
+
     void comm_init(const void* id128, int rank, int world);
     int world() const { return world_; }
 
@@ -154,6 +161,10 @@ private:
 
     // inference workspace
     Levels iw_;
+    struct DatasetImage { std::unique_ptr<DevBuf> rgb, labels; int h = 0, w = 0; };
+    std::vector<DatasetImage> dataset_;
+    DevBuf crop_jobs_, crop_scratch_, crop_overflow_;
+    void* crop_jobs_host_ = nullptr; size_t crop_jobs_host_bytes_ = 0;   // pinned
     DevBuf e_truth_, e_pred_, e_roots_, e_counts_, e_rgba_;   // evaluation / write-back scratch
     DevBuf i_up_, t_up_;   // the up-sampled tensor of a join that needs the bilinear resize (non-canonical input sizes)
     DevBuf i_x_, i_logits_, i_img_, i_labels_, canvas_, gains_dev_, seam_, det_dev_, seeds_, blob_parent_, blob_keep_;

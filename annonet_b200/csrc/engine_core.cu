@@ -105,6 +105,7 @@ Engine::~Engine()
     if (ev_unstaged_) cudaEventDestroy(ev_unstaged_);
     if (pinned_) cudaFreeHost(pinned_);
     if (loss_host_) cudaFreeHost(loss_host_);
+    if (crop_jobs_host_) cudaFreeHost(crop_jobs_host_);
     if (comm_stream_) cudaStreamDestroy(comm_stream_);
     if (copy_stream_) cudaStreamDestroy(copy_stream_);
     if (side_stream_) cudaStreamDestroy(side_stream_);

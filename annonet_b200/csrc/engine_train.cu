@@ -283,6 +283,66 @@ void Engine::train_step_host(const uint8_t* imgs, const void* labels, int n, int
     train_step_device(t_imgs_.as<uint8_t>(), t_labels_.p, n, h, w, update);
 }
 
+void Engine::dataset_clear()
+{
+    synchronize();
+    dataset_.clear();
+}
+
+int Engine::dataset_add(const uint8_t* rgb, const uint16_t* labels, int h, int w)
+{
+    if (!rgb || !labels || h < 1 || w < 1) throw std::invalid_argument("dataset_add: bad image");
+    AB_CUDA(cudaSetDevice(device_));
+    DatasetImage d;
+    d.rgb = std::make_unique<DevBuf>(); d.labels = std::make_unique<DevBuf>();
+    d.h = h; d.w = w;
+    d.rgb->reserve((size_t)h * w * 3);
+    d.labels->reserve((size_t)h * w * 2);
+    AB_CUDA(cudaMemcpyAsync(d.rgb->p, rgb, (size_t)h * w * 3, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaMemcpyAsync(d.labels->p, labels, (size_t)h * w * 2, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaStreamSynchronize(stream_));
+    dataset_.push_back(std::move(d));
+    return (int)dataset_.size() - 1;
+}
+
+void Engine::build_crops(const CropSpec* crops, int n, int dim, double class_weight, double image_weight, const uint8_t** imgs_dev, const void** labels_dev)
+{
+    if (n < 1 || dim < 1 || !crops) throw std::invalid_argument("build_crops: bad arguments");
+    AB_CUDA(cudaSetDevice(device_));
+    const size_t jb = sizeof(k::CropJob) * (size_t)n;
+    if (crop_jobs_host_bytes_ < jb) {
+        AB_CUDA(cudaStreamSynchronize(stream_));
+        if (crop_jobs_host_) cudaFreeHost(crop_jobs_host_);
+        AB_CUDA(cudaMallocHost(&crop_jobs_host_, jb));
+        crop_jobs_host_bytes_ = jb;
+    }
+    AB_CUDA(cudaEventSynchronize(ev_stage_));   // the previous batch's job table has left the pinned buffer
+    k::CropJob* J = (k::CropJob*)crop_jobs_host_;
+    for (int i = 0; i < n; ++i) {
+        const CropSpec& c = crops[i];
+        if (c.image < 0 || c.image >= (int)dataset_.size()) throw std::invalid_argument("build_crops: no such dataset image");
+        if (c.noise_level < 0 || c.noise_level > 255 || !(c.brightness > 0)) throw std::invalid_argument("build_crops: bad augmentation parameters");
+        const DatasetImage& d = dataset_[c.image];
+        k::CropJob& j = J[i];
+        j.image = d.rgb->as<uint8_t>(); j.labels = d.labels->as<uint16_t>(); j.h = d.h; j.w = d.w;
+        j.left = c.left; j.top = c.top; j.flip_lr = c.flip_lr; j.flip_ud = c.flip_ud;
+        j.brightness = c.brightness; j.noise_level = c.noise_level; j.seed = c.seed;
+        for (int q = 0; q < 3; ++q) j.color_offset[q] = c.color_offset[q];
+    }
+    crop_jobs_.reserve(jb);
+    crop_scratch_.reserve(k::crop_scratch_bytes(n));
+    crop_overflow_.reserve(256);
+    t_imgs_.reserve((size_t)n * dim * dim * 3);
+    t_labels_.reserve((size_t)n * dim * dim * 8);
+    AB_CUDA(cudaMemcpyAsync(crop_jobs_.p, J, jb, cudaMemcpyHostToDevice, stream_));
+    AB_CUDA(cudaEventRecord(ev_stage_, stream_));
+    k::build_crops(crop_jobs_.as<k::CropJob>(), n, dim, class_weight, image_weight, crop_scratch_.p, t_imgs_.as<uint8_t>(), t_labels_.p,
+                   crop_overflow_.as<unsigned int>(), stream_);
+    AB_CUDA(cudaGetLastError());
+    *imgs_dev = t_imgs_.as<uint8_t>();
+    *labels_dev = t_labels_.p;
+}
+
 double Engine::train_sync()
 {
     synchronize();

@@ -102,6 +102,23 @@ void argmax_labels(const float* planes, long long plane_stride, int K, long long
 // annonet_infer.cpp:214-239: blobs of equal non-zero labels (8-neighbourhood) without a seed are set to 0.
 // parent: h*w ints, keep: h*w bytes of scratch.  transposed_seeds: mirror the reference's (r, c) -> point(x = r, y = c) ->
 // blobs(y, x) seed lookup (annonet_infer.cpp:210,221) instead of the evidently intended same-pixel lookup.
+// ---- mini-batch assembly on the device (kernels_crop.cu; annonet_train_main.cpp:110-232, annonet_train.h:20-83) -----------
+struct CropJob {
+    const uint8_t* image;       // full image, u8 HWC rgb, resident on the device
+    const uint16_t* labels;     // its label map, u16 (65535 = ignore)
+    int h, w;                   // size of the full image
+    int left, top;              // crop window = [left, left + dim) x [top, top + dim); may leave the image (outpaint / ignore)
+    int flip_lr, flip_ud;
+    double brightness;          // multiplicative brightness change (1.0: none)
+    int noise_level;            // uniform integer noise in [-level, level] per channel (0: none)
+    unsigned seed;              // of this crop's noise
+    int color_offset[3];        // apply_random_color_offset's per-channel offsets (0: none)
+};
+size_t crop_scratch_bytes(int n);
+// out_img: u8 [n][dim][dim][3]; out_lab: weighted_label<uint16_t> [n][dim][dim] (8 bytes each); overflow_dev: counts labels >= 256
+void build_crops(const CropJob* jobs_dev, int n, int dim, double class_weight, double image_weight, void* scratch, uint8_t* out_img, void* out_lab,
+                 unsigned int* overflow_dev, cudaStream_t st);
+
 // ---- evaluation and write-back of annonet_infer_main.cpp (confusion matrices :91-272,482-491; result images :408-418) --------
 // connected blobs of equal non-zero labels (8-neighbourhood): roots[i] = -1 (background) or the blob's smallest pixel index
 void label_blobs(const uint16_t* labels, int h, int w, int* roots, uint8_t* scratch_bytes, cudaStream_t st);

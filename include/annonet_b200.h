@@ -197,6 +197,34 @@ typedef enum ab_layer_kind {
 } ab_layer_kind;
 ab_status ab_get_layer_types(ab_net* net, int32_t* kinds, int capacity, int* count);
 
+/* ---- device-resident dataset and mini-batch assembly ---------------------------------------------
+ * The reference's loader threads cut every crop on the CPU (annonet_train_main.cpp:110-232,520-553: extract_image_chip,
+ * outpaint, set_weights, flips, brightness, noise, colour offset) and the trainer copies it to the GPU.  Here the full images
+ * and label maps are uploaded once; per step the host sends only the random decisions and the crops and their weighted labels
+ * are written by kernels straight into the step's input buffers.  Crop windows may leave the image: pixels outside repeat
+ * the nearest image pixel (outpaint, annonet.h:74-120), labels outside are ignored (65535, weight 0).  Weights are
+ * set_weights(class_weight, image_weight) of each crop (annonet_train.h:20-83; class ids < 256 on this path).  Order of the
+ * augmentations as in the reference: crop -> weights -> flips -> brightness -> noise -> colour offset.  Noise is a
+ * reproducible function of (seed, pixel, channel), not dlib::rand's stream. */
+typedef struct ab_crop {
+    int32_t image;            /* index returned by ab_dataset_add */
+    int32_t left, top;        /* crop window [left, left + dim) x [top, top + dim) in image coordinates */
+    int32_t flip_lr, flip_ud;
+    double brightness;        /* multiplicative brightness change, 1.0 = none (annonet_train_main.cpp:198-221) */
+    int32_t noise_level;      /* uniform integer noise in [-level, level] per channel, 0 = none (:73-101) */
+    uint32_t seed;
+    int32_t color_offset[3];  /* per-channel offsets of dlib::apply_random_color_offset, 0 = none */
+} ab_crop;
+ab_status ab_dataset_clear(ab_net* net);
+ab_status ab_dataset_add(ab_net* net, const uint8_t* rgb_hwc, const uint16_t* labels, int h, int w, int* index);
+/* device memory handed out by the net (ab_build_crops) -> host, after the net's stream has drained */
+ab_status ab_copy_to_host(ab_net* net, void* dst_host, const void* src_dev, size_t bytes);
+/* crops -> u8 [n][dim][dim][3] and ab_wlabel [n][dim][dim] in device memory owned by the net (valid until the next call) */
+ab_status ab_build_crops(ab_net* net, const ab_crop* crops, int n, int dim, double class_weight, double image_weight,
+                         const void** imgs_dev, const void** labels_dev);
+/* ab_build_crops + ab_train_step_device: one asynchronous training step on a mini-batch cut on the device */
+ab_status ab_train_step_crops(ab_net* net, const ab_crop* crops, int n, int dim, double class_weight, double image_weight);
+
 /* data-parallel training: flat gradient arena for the caller's/engine's all-reduce
  * (multi_device_tensor_averager, tensor_tools.h:1609-1736 -> NCCL) */
 ab_status ab_gradient_arena(ab_net* net, void** grads_dev, size_t* count_floats);

@@ -718,6 +718,32 @@ def filter_detections(labels: np.ndarray, blended: np.ndarray, detection_levels:
     return out
 
 
+def crop_and_augment(image: np.ndarray, labels: np.ndarray, left: int, top: int, dim: int, class_weight: float, image_weight: float,
+                     flip_lr: bool = False, flip_ud: bool = False, brightness: float = 1.0, color_offset: Sequence[int] = (0, 0, 0)):
+    """randomly_crop_image, annonet_train_main.cpp:110-232, for given random decisions and further_downscaling_factor 1
+    (extract_image_chip with an unscaled dim x dim rectangle copies pixels; outside the image the chip is black and outpaint,
+    annonet.h:74-120, then repeats the nearest valid pixel; labels outside become label_to_ignore): crop -> set_weights ->
+    fliplr / flipud -> multiplicative brightness (tuc::round of the clamped product) -> colour offset
+    (random_color_transform.h:98-150: put_in_range(0, 255, v + offset)).  Noise (:73-101) is left out: it is a random stream.
+    Returns (u8 [dim, dim, 3], u16 labels [dim, dim], f32 weights [dim, dim])."""
+    h, w = labels.shape
+    ys, xs = top + np.arange(dim), left + np.arange(dim)
+    inside = ((ys >= 0) & (ys < h))[:, None] & ((xs >= 0) & (xs < w))[None, :]
+    cy, cx = np.clip(ys, 0, h - 1), np.clip(xs, 0, w - 1)
+    img = image[cy][:, cx].copy()
+    lab = np.where(inside, labels[cy][:, cx], LABEL_TO_IGNORE).astype(np.uint16)
+    wts = set_weights(lab, class_weight, image_weight)
+    if flip_lr:
+        img, lab, wts = img[:, ::-1], lab[:, ::-1], wts[:, ::-1]
+    if flip_ud:
+        img, lab, wts = img[::-1], lab[::-1], wts[::-1]
+    v = img.astype(np.float64)
+    if brightness != 1.0:
+        v = np.floor(np.clip(v * brightness, 0.0, 255.0) + 0.5)
+    v = np.clip(v + np.asarray(color_offset, dtype=np.float64).reshape(1, 1, 3), 0, 255)
+    return v.astype(np.uint8), np.ascontiguousarray(lab), np.ascontiguousarray(wts)
+
+
 def confusion_per_pixel(truth: np.ndarray, predicted: np.ndarray, k: int) -> np.ndarray:
     """confusion_matrix_per_pixel, annonet_infer_main.cpp:482-489: [truth][predicted] over the labelled pixels (truth != 65535)."""
     m = (truth < k) & (predicted < k)
