@@ -62,7 +62,7 @@ class _Tile(C.Structure):
 EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
-    "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_infer_tiled", "ab_infer_tiled_device",
+    "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_plan_bands", "ab_infer_tiled", "ab_infer_tiled_device",
     "ab_dataset_clear", "ab_dataset_add", "ab_build_crops", "ab_copy_to_host", "ab_train_step_crops", "ab_set_detection_levels", "ab_evaluate_labels", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
@@ -135,6 +135,15 @@ def get_tiles(width: int, height: int, max_tile_w: int, max_tile_h: int, overlap
     arr = (_Tile * max(n.value, 1))()
     _check(lib.ab_get_tiles(width, height, max_tile_w, max_tile_h, overlap_x, overlap_y, arr, n.value, C.byref(n)))
     return [dict(full=tuple(t.full), non_overlapping=tuple(t.non_overlapping), unique=tuple(t.unique)) for t in arr[:n.value]]
+
+
+def plan_bands(width: int, height: int, max_tile_w: int, max_tile_h: int, world: int, levels: int = 6):
+    """The band plan of a sharded annonet_infer() (engine_infer.cu / tiling.cpp plan_bands): per rank a dict with the tile
+    range [t0, t1), the image rows it owns (own0..own1, argmax) and the rows its tiles touch (f0..f1, private canvas)."""
+    out = (C.c_int * (6 * world))()
+    _check(lib.ab_plan_bands(width, height, max_tile_w, max_tile_h, levels, world, out))
+    keys = ("t0", "t1", "own0", "own1", "f0", "f1")
+    return [dict(zip(keys, out[6 * r:6 * r + 6])) for r in range(world)]
 
 
 def set_weights(labels: np.ndarray, class_weight: float, image_weight: float) -> np.ndarray:

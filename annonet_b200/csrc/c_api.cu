@@ -167,6 +167,20 @@ ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, in
     });
 }
 
+ab_status ab_plan_bands(int width, int height, int max_tile_w, int max_tile_h, int levels, int world, int* out)
+{
+    return guarded([&] {
+        if (world < 1 || levels < 1 || levels > 12 || !out) throw std::invalid_argument("ab_plan_bands: bad arguments");
+        const int ov = (1 << (levels + 1)) - 1;
+        const std::vector<ab::Tile> t = ab::get_tiles(width, height, max_tile_w, max_tile_h, ov, ov);
+        const std::vector<ab::Band> b = ab::plan_bands(t, world, levels);
+        for (int r = 0; r < world; ++r) {
+            const int v[6] = {b[r].t0, b[r].t1, b[r].own0, b[r].own1, b[r].f0, b[r].f1};
+            std::memcpy(out + 6 * r, v, sizeof v);
+        }
+    });
+}
+
 ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, int max_tile_w, int max_tile_h, const double* gains,
                          int ngains, uint16_t* labels_host, float* blended_host)
 {

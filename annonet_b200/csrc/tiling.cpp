@@ -72,4 +72,51 @@ void set_weights(const uint16_t* labels, int h, int w, double class_weight, doub
     for (size_t i = 0; i < n; ++i) out[i] = labels[i] == 65535 ? 0.f : (float)lw[labels[i]];
 }
 
+
+namespace {
+// smallest size >= minimum that survives `levels` pool/up-conv round trips: 2^levels * k + (2^levels - 1) (NetPimpl.cpp:246-285)
+int band_input_dimension(int minimum, int levels)
+{
+    const int m = 1 << levels;
+    int k = 1;
+    while (m * k + m - 1 < minimum) ++k;
+    return m * k + m - 1;
+}
+}  // namespace
+
+// Tiles arrive row by row (tiling.cpp:57-83).  Rows are dealt to the ranks as contiguous bands of near-equal COST (the
+// pixels the net actually runs: every tile is enlarged to 64k + 63) -- not round-robin: neighbouring rows share a seam, so
+// a band exchanges at most two seams, and 19 rows over 8 ranks cost max 3 rows either way but far less traffic.
+std::vector<Band> plan_bands(const std::vector<Tile>& tiles, int world, int levels)
+{
+    std::vector<int> row_start;   // first tile of each tile row
+    std::vector<double> row_cost;
+    for (size_t i = 0; i < tiles.size(); ++i) {
+        if (i == 0 || tiles[i].full[1] != tiles[i - 1].full[1]) { row_start.push_back((int)i); row_cost.push_back(0); }
+        const int fw = tiles[i].full[2] - tiles[i].full[0] + 1, fh = tiles[i].full[3] - tiles[i].full[1] + 1;
+        row_cost.back() += (double)band_input_dimension(fw, levels) * band_input_dimension(fh, levels);
+    }
+    const int rows = (int)row_start.size();
+    row_start.push_back((int)tiles.size());
+    double total = 0;
+    for (double c : row_cost) total += c;
+    std::vector<Band> bands(world);
+    int j = 0;
+    double done = 0;
+    for (int r = 0; r < world; ++r) {
+        const int ja = j;
+        const double target = total * (r + 1) / world;
+        // take rows while that brings the running cost closer to this rank's share of the total; leave enough rows for the rest
+        while (j < rows && (rows - j > world - 1 - r) && (j == ja ? true : std::abs(done + row_cost[j] - target) <= std::abs(done - target))) done += row_cost[j++];
+        if (r == world - 1) while (j < rows) done += row_cost[j++];
+        if (j == ja && j < rows && rows - j >= world - r) done += row_cost[j++];
+        Band& b = bands[r];
+        b.t0 = row_start[ja]; b.t1 = row_start[j];
+        if (b.empty()) continue;
+        b.own0 = tiles[b.t0].non_overlapping[1]; b.own1 = tiles[b.t1 - 1].non_overlapping[3];
+        b.f0 = tiles[b.t0].full[1]; b.f1 = tiles[b.t1 - 1].full[3];
+    }
+    return bands;
+}
+
 }  // namespace ab

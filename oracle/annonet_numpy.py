@@ -627,7 +627,7 @@ def _get_t(c, first_possible, first_in, last_in, last_possible):
 
 
 def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int, gains: Sequence[float] = (),
-                  overlap: Optional[int] = None, return_blended: bool = False, forward_fn=None, rank: int = 0, world: int = 1):
+                  overlap: Optional[int] = None, return_blended: bool = False, forward_fn=None, tile_range: Optional[Tuple[int, int]] = None):
     """annonet_infer(), annonet_infer.cpp:32-185 (without the detection-level blob filter):
     tiles -> enlarge to the recommended size around the centre -> clamp-to-edge fill (outpaint,
     annonet.h:74-120) -> Forward -> blend (double ramps, float accumulate) -> argmax."""
@@ -636,13 +636,10 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
     ov = overlap if overlap is not None else (1 << (levels + 1)) - 1
     tiles = get_tiles(w, h, max_tile_w, max_tile_h, ov, ov)
     blended = None
-    row, last_top = -1, None
-    for tile in tiles:
+    for ti, tile in enumerate(tiles):
         fl, ft, fr, fb = tile["full"]
-        # multi-GPU sharding of the engine: tile rows are dealt round-robin, canvases are summed afterwards
-        if ft != last_top:
-            row, last_top = row + 1, ft
-        if world > 1 and row % world != rank:
+        # multi-GPU sharding of the engine: a rank runs the tiles [t0, t1) of its band into a private canvas
+        if tile_range is not None and not (tile_range[0] <= ti < tile_range[1]):
             continue
         ul, ut, ur, ub = tile["unique"]
         fw, fh = fr - fl + 1, fb - ft + 1
@@ -674,6 +671,8 @@ def annonet_infer(anet: Net, image: np.ndarray, max_tile_w: int, max_tile_h: int
         dst = blended[:, y0:y1 + 1, x0:x1 + 1]
         acc = (dst.astype(np.float64) + t[None] * src.astype(np.float64)).astype(F32)  # `out += t * in` with float out
         dst[...] = np.where(unique[None], src, acc)
+    if blended is None:
+        return (None, None) if return_blended else None
     labels = to_label(blended, gains)
     return (labels, blended) if return_blended else labels
 

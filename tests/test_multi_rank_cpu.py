@@ -1,7 +1,8 @@
-"""world_size-2 checks of the multi-GPU host logic on CPU (gloo): the tile-row sharding of tiled inference
-(rank r blends the tile rows r, r + world, ... into a private canvas, canvases are summed by one
-all-reduce, every rank runs the argmax) must reproduce the single-process annonet_infer() result, and the data-parallel
-gradient exchange (sum all-reduce of the flat arena, 1/world folded into the update) must equal the reference's
+"""world_size-2 checks of the multi-GPU host logic on CPU (gloo), following the engine's own protocol (DESIGN.md §6,
+engine_infer.cu): the band plan comes from the library (ab_plan_bands, host only), every rank blends the tiles of its band
+into a private canvas, the seam strips go to the rank that owns the rows (send/recv, added there), every rank runs the argmax
+of its rows and the label strips are gathered -- the result must be the single-process annonet_infer() label map.  And the
+data-parallel gradient exchange (sum all-reduce of the flat arena, 1/world folded into the update) must equal the reference's
 per-device mean (trainer.h:797-801)."""
 import os
 import socket
@@ -35,15 +36,49 @@ def _image():
     return np.random.default_rng(5).integers(0, 256, size=(H, W, 3), dtype=np.uint8)
 
 
+def _strips(bands, rank):
+    """(outgoing, incoming) seam strips of a rank as (peer, y0, y1), image rows inclusive -- engine_infer.cu's Strip lists"""
+    me = bands[rank]
+    live = [r for r, b in enumerate(bands) if b["t1"] > b["t0"]]
+    prev = max([r for r in live if r < rank], default=-1)
+    nxt = min([r for r in live if r > rank], default=-1)
+    out, inc = [], []
+    if me["t1"] > me["t0"]:
+        if prev >= 0 and me["f0"] < me["own0"]: out.append((prev, me["f0"], me["own0"] - 1))
+        if nxt >= 0 and me["f1"] > me["own1"]: out.append((nxt, me["own1"] + 1, me["f1"]))
+        if prev >= 0 and bands[prev]["f1"] >= me["own0"]: inc.append((prev, me["own0"], bands[prev]["f1"]))
+        if nxt >= 0 and bands[nxt]["f0"] <= me["own1"]: inc.append((nxt, bands[nxt]["f0"], me["own1"]))
+    return out, inc
+
+
 def _worker(rank, world, port, out):
+    import annonet_b200 as ab
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         anet = df.Net(layers=[{"type": "loss"}, {"type": "con", "num_filters": K}], levels=6)
-        _, canvas = on.annonet_infer(anet, _image(), TILE, TILE, return_blended=True, forward_fn=_fake_forward, rank=rank, world=world)
-        t = torch.from_numpy(canvas.copy())
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)          # the one exchange step of sharded inference
-        labels = on.to_label(t.numpy(), ())
+        bands = ab.plan_bands(W, H, TILE, TILE, world)
+        me = bands[rank]
+        _, canvas = on.annonet_infer(anet, _image(), TILE, TILE, return_blended=True, forward_fn=_fake_forward, tile_range=(me["t0"], me["t1"]))
+        assert not canvas[:, :me["f0"]].any() and not canvas[:, me["f1"] + 1:].any()      # a band canvas spans f0..f1 only
+        sends, recvs = _strips(bands, rank)
+        reqs = [dist.isend(torch.from_numpy(np.ascontiguousarray(canvas[:, y0:y1 + 1])), peer) for peer, y0, y1 in sends]
+        for peer, y0, y1 in recvs:
+            t = torch.empty((K, y1 - y0 + 1, W), dtype=torch.float32)
+            dist.recv(t, peer)
+            canvas[:, y0:y1 + 1] += t.numpy()
+        for r in reqs:
+            r.wait()
+        labels = np.zeros((H, W), dtype=np.uint16)
+        labels[me["own0"]:me["own1"] + 1] = on.to_label(canvas[:, me["own0"]:me["own1"] + 1], ())
+        for r in range(world):     # the label strips are broadcast by their owners
+            t = torch.from_numpy(labels[bands[r]["own0"]:bands[r]["own1"] + 1].astype(np.int32))
+            dist.broadcast(t, r)
+            labels[bands[r]["own0"]:bands[r]["own1"] + 1] = t.numpy().astype(np.uint16)
+        own = np.zeros_like(canvas)
+        own[:, me["own0"]:me["own1"] + 1] = canvas[:, me["own0"]:me["own1"] + 1]
+        t = torch.from_numpy(own)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)          # (test only: assemble the owned rows to compare the canvas too)
         # data-parallel gradient exchange on a fake arena: sum all-reduce, then 1/world inside the update
         g = torch.from_numpy(np.random.default_rng(100 + rank).normal(size=1000).astype(np.float32))
         gs = g.clone()
@@ -68,10 +103,27 @@ def test_sharded_inference_and_gradient_exchange_world2(tmp_path):
     assert np.allclose(got["gsum"] / 2, got["gmean"], rtol=0, atol=1e-6)
 
 
-def test_tile_rows_partition_the_tiles():
-    tiles = on.get_tiles(W, H, TILE, TILE, 127, 127)
-    tops = sorted({t["full"][1] for t in tiles})
-    for world in (2, 4, 8):
-        owner = [tops.index(t["full"][1]) % world for t in tiles]
-        assert sorted(set(owner)) == list(range(min(world, len(tops))))
-        assert sum(owner.count(r) for r in range(world)) == len(tiles)
+def test_bands_partition_the_tiles_and_the_rows():
+    import annonet_b200 as ab
+    for (w, h, tile) in ((W, H, TILE), (16384, 16384, 1024), (300, 5000, 256), (200, 200, 512)):
+        tiles = on.get_tiles(w, h, tile, tile, 127, 127)
+        assert tiles == ab.get_tiles(w, h, tile, tile, 127, 127)
+        tops = sorted({t["full"][1] for t in tiles})
+        cost = {}
+        for t in tiles:
+            fw, fh = t["full"][2] - t["full"][0] + 1, t["full"][3] - t["full"][1] + 1
+            cost[t["full"][1]] = cost.get(t["full"][1], 0) + on.recommended_input_dimension(fw, 6) * on.recommended_input_dimension(fh, 6)
+        for world in (1, 2, 3, 4, 8):
+            bands = ab.plan_bands(w, h, tile, tile, world)
+            live = [b for b in bands if b["t1"] > b["t0"]]
+            assert len(live) == min(world, len(tops))                       # nobody idles while there are rows to deal
+            assert live[0]["t0"] == 0 and live[-1]["t1"] == len(tiles)
+            assert all(a["t1"] == b["t0"] for a, b in zip(live, live[1:]))  # contiguous, in order
+            assert live[0]["own0"] == 0 and live[-1]["own1"] == h - 1
+            assert all(a["own1"] + 1 == b["own0"] for a, b in zip(live, live[1:]))   # owned rows tile the image
+            for b in live:
+                assert b["f0"] <= b["own0"] <= b["own1"] <= b["f1"]
+                assert tiles[b["t0"]]["full"][1] != tiles[b["t0"] - 1]["full"][1] if b["t0"] else True   # cut between tile rows
+            # balance: no band costs more than the ideal share plus one tile row
+            per = [sum(cost[y] for y in {t["full"][1] for t in tiles[b["t0"]:b["t1"]]}) for b in live]
+            assert max(per) <= sum(cost.values()) / len(live) + max(cost.values()) + 1e-9
