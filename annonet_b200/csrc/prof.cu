@@ -15,7 +15,7 @@ std::vector<Sample> g_samples;
 std::vector<cudaEvent_t> g_free;
 
 const char* kNames[F_COUNT] = {"conv3x3", "conv1x1", "up_cont", "wgrad", "bias_grad", "bn_mish", "max_pool", "loss", "argmax",
-                               "blend", "input", "optimizer", "pack", "conv_tc", "wgrad_tc", "ew_bf16"};
+                               "blend", "input", "optimizer", "pack", "conv_tc", "wgrad_tc", "ew_f16"};
 
 cudaEvent_t get_event()
 {
