@@ -63,7 +63,7 @@ EXPORTS = [
     "ab_version", "ab_last_error", "ab_free", "ab_net_create", "ab_net_destroy", "ab_net_clone", "ab_net_info",
     "ab_net_init_random", "ab_net_load_dlib", "ab_net_load_dlib_prefix", "ab_net_save_dlib", "ab_dlib_transcode", "ab_required_input_dimension",
     "ab_recommended_input_dimension", "ab_forward", "ab_process", "ab_get_tiles", "ab_plan_bands", "ab_infer_tiled", "ab_infer_tiled_device",
-    "ab_dataset_clear", "ab_dataset_add", "ab_build_crops", "ab_copy_to_host", "ab_train_step_crops", "ab_set_detection_levels", "ab_evaluate_labels", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
+    "ab_dataset_clear", "ab_dataset_add", "ab_build_crops", "ab_copy_to_host", "ab_train_step_crops", "ab_set_detection_levels", "ab_evaluate_labels", "ab_confusion_per_pixel_noalloc", "ab_render_labels", "ab_get_layer_momentum", "ab_set_layer_momentum", "ab_get_layer_types", "ab_set_hyper", "ab_get_hyper", "ab_train_step_async", "ab_train_step_device",
     "ab_train_sync", "ab_compute_gradients", "ab_get_logits", "ab_get_level_tensor", "ab_get_layer_gradient", "ab_get_layer_params",
     "ab_gradient_arena", "ab_comm_unique_id", "ab_comm_init", "ab_set_weights", "ab_stream", "ab_kernel_launches",
     "ab_device_synchronize", "ab_profile_enable", "ab_profile_read",
@@ -144,6 +144,17 @@ def plan_bands(width: int, height: int, max_tile_w: int, max_tile_h: int, world:
     _check(lib.ab_plan_bands(width, height, max_tile_w, max_tile_h, levels, world, out))
     keys = ("t0", "t1", "own0", "own1", "f0", "f1")
     return [dict(zip(keys, out[6 * r:6 * r + 6])) for r in range(world)]
+
+
+NOALLOC_MAX_CLASSES = 64
+
+
+def confusion_per_pixel_noalloc(truth_dev: int, predicted_dev: int, n: int, class_count: int, per_pixel_dev: int, stream: int = 0) -> None:
+    """ab_confusion_per_pixel_noalloc: the per-pixel confusion matrix of evaluate_labels() on DEVICE pointers (plain ints
+    here), accumulating in the library's static device scratch -- the call allocates nothing.  No counterpart in the
+    reference.  Asynchronous on `stream` (a cudaStream_t as int)."""
+    _check(lib.ab_confusion_per_pixel_noalloc(C.c_void_p(truth_dev), C.c_void_p(predicted_dev), C.c_longlong(n), C.c_int(class_count),
+                                              C.c_void_p(per_pixel_dev), C.c_void_p(stream)))
 
 
 def set_weights(labels: np.ndarray, class_weight: float, image_weight: float) -> np.ndarray:

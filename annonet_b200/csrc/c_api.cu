@@ -10,6 +10,10 @@
 #include <cstring>
 
 namespace ab { void nccl_unique_id(void* id128); }
+namespace ab { namespace noalloc {   // noalloc.cu
+int max_classes();
+void confusion_per_pixel(const uint16_t* truth_dev, const uint16_t* pred_dev, long long n, int K, unsigned long long* out_dev, cudaStream_t st);
+} }
 
 struct ab_net {
     std::unique_ptr<ab::Engine> eng;
@@ -194,6 +198,16 @@ ab_status ab_evaluate_labels(ab_net* net, const uint16_t* truth, const uint16_t*
         if (!truth || !predicted || !per_pixel || h < 1 || w < 1) throw std::invalid_argument("bad arguments");
         static_assert(sizeof(uint64_t) == sizeof(unsigned long long), "64-bit counters");
         E(net).evaluate_labels(truth, predicted, h, w, class_count, (unsigned long long*)per_pixel, (unsigned long long*)per_region);
+    });
+}
+
+ab_status ab_confusion_per_pixel_noalloc(const uint16_t* truth_dev, const uint16_t* predicted_dev, long long n, int class_count,
+                                         uint64_t* per_pixel_dev, void* stream)
+{
+    return guarded([&] {
+        static_assert(AB_NOALLOC_MAX_CLASSES == 64, "keep the header's limit and noalloc.cu's array in step");
+        if (ab::noalloc::max_classes() != AB_NOALLOC_MAX_CLASSES) throw ab::state_error("noalloc scratch size and header limit disagree");
+        ab::noalloc::confusion_per_pixel(truth_dev, predicted_dev, n, class_count, (unsigned long long*)per_pixel_dev, (cudaStream_t)stream);
     });
 }
 

@@ -149,6 +149,20 @@ ab_status ab_infer_tiled(ab_net* net, const uint8_t* image_hwc, int h, int w, in
  * labelled.  per_pixel / per_region: class_count^2 counters [truth][predicted]; per_region may be NULL. */
 ab_status ab_evaluate_labels(ab_net* net, const uint16_t* truth, const uint16_t* predicted, int h, int w, int class_count,
                              uint64_t* per_pixel, uint64_t* per_region);
+/* The per-pixel confusion matrix of ab_evaluate_labels again, for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * The call allocates nothing -- no cudaMalloc / cudaFree, no allocating library routine: the counters it accumulates
+ * into live in a static __device__ array of the library (64 x 64 x 8 bytes = 32 KB, held by every GPU that loads the library
+ * until the process exits).  truth_dev / predicted_dev: n uint16 each, DEVICE memory of the current device (65535 = not
+ * labelled); per_pixel_dev: class_count^2 uint64 [truth][predicted], DEVICE memory; stream: the cudaStream_t to launch on (NULL
+ * = the default stream).  Asynchronous: the result is complete when the stream's work is.
+ * Limit: class_count <= AB_NOALLOC_MAX_CLASSES (64); anything larger returns AB_ERR_ARGUMENT with the limit in ab_last_error().
+ * The array is shared by every call on that GPU and keeps the last call's contents; each call clears what it uses first, on
+ * `stream`.  Calls that overlap on the GPU (other streams, unordered host threads) RACE on it: serialise them.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress); make it outside a stream capture. */
+#define AB_NOALLOC_MAX_CLASSES 64
+ab_status ab_confusion_per_pixel_noalloc(const uint16_t* truth_dev, const uint16_t* predicted_dev, long long n, int class_count,
+                                         uint64_t* per_pixel_dev, void* stream);
 /* The result image of annonet_infer_main.cpp:408-418: resize_label_image (nearest neighbour, annonet.cpp:132-141) to
  * out_h x out_w fused with index_label_image_to_rgba_label_image (:74-86); palette_rgba: class_count x 4 bytes,
  * rgba_out: out_h*out_w*4 bytes (host; the caller writes the PNG). */
