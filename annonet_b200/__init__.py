@@ -271,11 +271,14 @@ class RuntimeNet(_Net):
         return recommended_input_dimension(minimum)
 
     def infer(self, image: np.ndarray, max_tile_w: int, max_tile_h: int, gains: Optional[Sequence[float]] = None,
-              return_blended: bool = False):
-        """annonet_infer() (annonet_infer.cpp:32-185) without detection levels."""
+              return_blended: bool = False, labels_out: Optional[np.ndarray] = None):
+        """annonet_infer() (annonet_infer.cpp:32-185) without detection levels.  labels_out: an optional contiguous uint16 [h, w]
+        array to receive the label map (e.g. a view of pinned memory)."""
         image = np.ascontiguousarray(image, dtype=np.uint8)
         h, w, _ = image.shape
-        labels = np.empty((h, w), dtype=np.uint16)
+        if labels_out is not None:
+            assert labels_out.dtype == np.uint16 and labels_out.shape == (h, w) and labels_out.flags["C_CONTIGUOUS"]
+        labels = labels_out if labels_out is not None else np.empty((h, w), dtype=np.uint16)
         blended = np.empty((self.info()["class_count"], h, w), dtype=np.float32) if return_blended else None
         g, ng = _gains(gains)
         _check(lib.ab_infer_tiled(self._h, _ptr(image), h, w, max_tile_w, max_tile_h, _ptr(g) if g is not None else None, ng,

@@ -82,6 +82,12 @@ __device__ __forceinline__ void tmem_ld_fence(float v[16])
                       "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]) :: "memory");
 }
 
+// p[0..7] += v[0..7] (fp16, round to nearest) as one 16-byte reduction performed at the L2; p is 16-byte aligned
+__device__ __forceinline__ void red_add_h8(h16* p, const uint32_t v[4])
+{
+    asm volatile("red.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+}
+
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, LBO (unused for
 // swizzled K-major) = 1, SBO = 8 rows * pitch, version 1, layout type 6/4/2 for 32/64/128-byte swizzle.
 __device__ __forceinline__ uint64_t smem_desc_hi(int pitch)
@@ -367,7 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         }
                     }
                     const int co0 = n0 + j;
-                    if (co0 >= L.cout || (L.dbg & 4)) continue;   // (uniform) padding columns only; AB_TC_DBG & 4: no stores
+                    if (co0 >= L.cout || (L.dbg & 4) || ((L.dbg & 8) && L.mode == OUT_F32_NHWC)) continue;   // (uniform) padding columns only; AB_TC_DBG & 4: no stores, & 8: no fp32 z stores
 #pragma unroll
                     for (int i4 = 0; i4 < 4; ++i4) {
                         const float4 b = *reinterpret_cast<const float4*>(&s_bias[co0 + 4 * i4]);
@@ -425,7 +431,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
                         const bool cok = co0 + ho < L.cout;
                         h16* oa = (h16*)L.out + posA * L.out_ctot + L.out_c0 + co0 + ho;
                         h16* ob = (h16*)L.out + posB * L.out_ctot + L.out_c0 + co0 + ho;
-                        if (accum) {
+                        if (accum && !(L.dbg & 16)) {
+                            // accumulate with ONE 16-byte reduction per half row (REDG.E.ADD.F16x8): the add happens in L2, nothing comes
+                            // back to the SM, so the epilogue does not wait for the old value (the read-modify-write below cost ~1.1 ms of
+                            // the step's conv time; AB_TC_DBG & 16 selects it again).  The addend is saturated, the sum is rounded once more
+                            // in fp16 -- gradients only, which the loss scale keeps far from the fp16 range limits.
+                            float rcv[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) rcv[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i] : v[8 + i], 1);
+                            __half2 ra[4], rb[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const float a0 = odd ? rcv[2 * i] : v[2 * i], a1 = odd ? rcv[2 * i + 1] : v[2 * i + 1];
+                                const float b0 = odd ? v[8 + 2 * i] : rcv[2 * i], b1 = odd ? v[8 + 2 * i + 1] : rcv[2 * i + 1];
+                                ra[i] = sat_half2(a0, a1);
+                                rb[i] = sat_half2(b0, b1);
+                            }
+                            if (okA && cok) red_add_h8(oa, reinterpret_cast<const uint32_t*>(ra));
+                            if (okB && cok) red_add_h8(ob, reinterpret_cast<const uint32_t*>(rb));
+                        } else if (accum) {
                             uint4 oldA = make_uint4(0, 0, 0, 0), oldB = make_uint4(0, 0, 0, 0);
                             if (okA && cok) oldA = *reinterpret_cast<const uint4*>(oa);
                             if (okB && cok) oldB = *reinterpret_cast<const uint4*>(ob);
