@@ -604,4 +604,14 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to stdout on the first
+    # communicator): descriptor 1 goes to stderr for the whole run, and only our own print()s reach the real stdout.
+    sys.stdout.flush()
+    _real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _real
+    try:
+        _rc = main()
+    finally:
+        _real.flush()
+    sys.exit(_rc)

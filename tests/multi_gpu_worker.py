@@ -82,19 +82,32 @@ def case_infer(rank, world, local, precision):
     gains = [0.0, 0.05, -0.05, 0.0, 0.1, 0.0, -0.1, 0.02]
     one = ab.RuntimeNet(local, precision)
     one.Deserialize(data)
-    ref_labels, ref_blend = one.infer(img, 512, 512, gains=gains, return_blended=True)
     rt = ab.RuntimeNet(local, precision)
     rt.Deserialize(data)
     rt.comm_init(unique_id(rank), rank, world)
+    # Tiles run alone (AB_INFER_BATCH=1, and always on the fp32 path): a tile's logits do not depend on which rank runs it, only
+    # the seams are summed in another order (float addition is not associative), so at most exact ties flip.  With the default
+    # batching of equal-sized tiles (tensor-core path) a band forms other batches than the whole image does, the convolution
+    # tiling follows the batch size, the fp32 accumulation order follows the tiling and fp16-rounded activations can move by an
+    # ulp: labels may then differ where the two best classes are nearly tied, and nowhere else.
+    batched = precision == ab.AB_PRECISION_F16 and os.environ.get("AB_INFER_BATCH", "8") != "1"
     for tile in (512, 300):
-        ref_labels = one.infer(img, tile, tile, gains=gains)
+        ref_labels, ref_blend = one.infer(img, tile, tile, gains=gains, return_blended=True)
         labels = rt.infer(img, tile, tile, gains=gains)
         agree = float(np.mean(labels == ref_labels))
         copies = gather(labels.astype(np.int32))
         for c in copies:
             assert np.array_equal(c, copies[0]), "ranks returned different label maps"
-        # seams are summed in a different order than on one GPU (float addition is not associative): exact ties may flip
-        assert agree >= 0.99999, f"tile {tile}: sharded labels agree on {agree:.6f} of the pixels"
+        if not batched:
+            assert agree >= 0.99999, f"tile {tile}: sharded labels agree on {agree:.6f} of the pixels"
+        else:
+            scores = ref_blend + np.asarray(gains, np.float32)[:, None, None]
+            top2 = np.sort(scores, axis=0)[-2:]
+            margin = (top2[1] - top2[0])[labels != ref_labels]
+            bound = 5e-3 * float(np.abs(ref_blend).max())
+            assert agree >= 0.999, f"tile {tile}: sharded labels agree on {agree:.6f} of the pixels"
+            assert margin.size == 0 or float(margin.max()) < bound, \
+                f"tile {tile}: a label differs where the one-GPU margin is {float(margin.max()):.3e} (near-tie bound {bound:.3e})"
         if rank == 0:
             print(f"OK infer precision {precision} tile {tile}: {world} ranks, labels agree with one GPU on {agree:.6f} of {labels.size} pixels")
 

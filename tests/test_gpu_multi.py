@@ -44,3 +44,8 @@ def test_data_parallel_training_two_ranks_eager():
 @pytest.mark.parametrize("precision", ["f16", "fp32"])
 def test_sharded_inference_two_ranks(precision):
     _run("infer", precision)
+
+
+def test_sharded_inference_two_ranks_unbatched_tiles_is_exact():
+    """every tile alone: the band protocol itself must reproduce the one-GPU label map (up to exact ties at the seams)"""
+    _run("infer", "f16", env={"AB_INFER_BATCH": "1"})
