@@ -121,7 +121,10 @@ void Engine::tc_ensure_train(int n, int h, int w)
     zero_reserve(T.glogits16, (size_t)T.tw.geo[0].positions() * Kp * 2);
     zero_reserve(T.bwd_packs, bwd_elems * 2);
     zero_reserve(T.train_packs, tp_elems * 2);
-    T.sums.reserve(sizeof(double) * 2 * cmax);
+    // batch-statistics sums (forward) and backward reduction sums: one slot per layer and pass, all cleared by ONE memset at the
+    // start of a step
+    T.sums_slot = (size_t)2 * cmax;
+    T.sums.reserve(sizeof(double) * T.sums_slot * 2 * plan_.groups.size());
     T.sums_side.reserve(sizeof(double) * 2 * cmax);
     T.bias_tmp.reserve(sizeof(float) * 256);
     T.wscratch.reserve(tc::wgrad_tc_scratch_floats() * 4);
@@ -392,6 +395,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
 
     // h16 filter packs of both directions from the fp32 master parameters
     const tc::PackJob* jobs = T.pack_jobs.as<tc::PackJob>();
+    AB_CUDA(cudaMemsetAsync(T.sums.p, 0, sizeof(double) * T.sums_slot * 2 * plan_.groups.size(), stream_));
     tc::pack_filters_batched(P, T.train_packs.as<h16>(), jobs, T.n_fwd_jobs, T.max_pack_elems, stream_);
     tc::pack_filters_batched(P, T.bwd_packs.as<h16>(), jobs + T.n_fwd_jobs, T.n_pack_jobs - T.n_fwd_jobs, T.max_pack_elems, stream_);
     T.fwd_packs_valid = false;   // (the inference packs no longer match the parameters once the optimizer has run)
@@ -432,7 +436,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         const Geo& geo = T.tw.geo[ol];
         // dead layers (computed, never consumed: NetStructure.h:41-55) only feed their own running statistics: side stream
         cudaStream_t fs = g.dead ? fork_side() : stream_;
-        double* sums = fs == stream_ ? T.sums.as<double>() : T.sums_side.as<double>();
+        double* sums = T.sums.as<double>() + T.sums_slot * (2 * gi);
         if (g.pool_input)
             tc::maxpool_nhwc(T.tw.level[g.in_level].as<h16>(), plan_.level_channels[g.in_level], g.in_c0, g.cin, T.tw.geo[g.in_level],
                              T.tw.pool.as<h16>() + T.tw.pool_off[gi], geo, fs, T.tw.pool_arg.as<uint8_t>() + T.tw.pool_off[gi],
@@ -443,7 +447,6 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
         const bool fused_stats = g.dlib_bn >= 0 && !no_fused_stats && t.fwd.size() == 1 && t.fwd[0].mode == tc::OUT_F32_NHWC &&
                                  t.fwd[0].nblk == 16 * t.fwd[0].nsum && t.fwd[0].npad_total == 16 * t.fwd[0].nsum;
         if (fused_stats) {
-            k::fill_zero((void*)sums, sizeof(double) * 2 * g.cout, fs);
             t.fwd[0].stat_sums = sums;
             t.fwd[0].stat_mish = g.has_mish && !g.bn_first;
         }
@@ -455,7 +458,7 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
             float* stats = t_stats_.as<float>() + stats_off_[gi];
             float* rmean = running_.as<float>() + running_off_[gi];
             const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
-            if (!fused_stats) tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, sums, fs, down);
+            if (!fused_stats) tc::bn_stats_nhwc(z, geo, g.has_mish && mish_first, sums, fs, down, 1);
             const double m = (double)((long long)n * geo.H * geo.W);
             const float eps = (float)model_.layers[g.dlib_bn].eps;
             if (g.dead) {
@@ -512,9 +515,9 @@ void Engine::tc_train_body(const uint8_t* imgs_dev, const void* labels_dev, int 
                 const tc::ViewF z{T.z.as<float>() + t.z_off, g.cout, 0, g.cout};
                 const View dzv{T.dz.as<h16>() + t.z_off, g.cout, 0, g.cout};
                 const View gy{T.tg.level[g.out_level].as<h16>(), plan_.level_channels[g.out_level], g.out_c0, g.cout};
-                tc::bn_backward_reduce_nhwc(z, gy, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
-                                            stream_, down);
-                tc::bn_backward_apply_nhwc(z, gy, dzv, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, T.sums.as<double>(),
+                double* red = T.sums.as<double>() + T.sums_slot * (2 * gi + 1);
+                tc::bn_backward_reduce_nhwc(z, gy, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, red, stream_, down, 1);
+                tc::bn_backward_apply_nhwc(z, gy, dzv, geo, mish_first, g.has_mish, P + g.bn_off, P + g.bn_off + g.cout, stats, red,
                                            G + g.bn_off, G + g.bn_off + g.cout, G + g.b_off, stream_, 0, unscale);
             } else {
                 // bias gradient = channel sums of the gradient at the conv output (layers.h:226, cpu_dlib.cpp:470-504)

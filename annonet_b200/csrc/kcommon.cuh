@@ -4,6 +4,7 @@
 #include "prof.h"
 
 #include <atomic>
+#include <cstdlib>
 
 namespace ab {
 namespace k {
@@ -24,6 +25,40 @@ inline int num_sms()
         return v;
     }();
     return n;
+}
+
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------------------------
+// The training step is ~370 dependent launches of 5..300 us; between two of them the GPU drains, launches and fills again.
+// A kernel launched with launch_pdl() may be made resident while its predecessor in the stream is still running; it must call
+// pdl_enter() BEFORE its first global-memory access: that blocks until the predecessor has completed and its writes are
+// visible (griddepcontrol.wait), then lets its own successor start becoming resident (griddepcontrol.launch_dependents -- after
+// the wait, so that completion of a kernel always implies completion of everything before it in the stream).  Launched
+// without the attribute (AB_NO_PDL=1, or the first kernel after a memset / event) both instructions are no-ops.
+__device__ __forceinline__ void pdl_enter()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+inline bool pdl_enabled()
+{
+    static const bool on = !(getenv("AB_NO_PDL") && atoi(getenv("AB_NO_PDL")) != 0);
+    return on;
+}
+
+// kernel<<<grid, block, smem, st>>>(args...) with the programmatic-stream-serialization attribute.  ONLY for kernels that call
+// pdl_enter() first thing.
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 // mish_: y = x - 2x/(e^2 + 2e + 2), e = exp(x)   (cpu_dlib.cpp:1510-1523; fp32 exp overflow -> y = x)

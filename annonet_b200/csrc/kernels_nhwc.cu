@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_kernel(const h16* __restrict
                                                            h16* __restrict__ out, int Ho, int Wo, uint8_t* __restrict__ arg, long long in_lo,
                                                            long long out_lo)
 {
+    k::pdl_enter();
     const long long total = (long long)N * Ho * Wo * C8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
@@ -129,7 +130,7 @@ void maxpool_nhwc(const h16* in, int in_ctot, int c0, int C, const Geo& gi, h16*
 {
     const long long n = (long long)go.N * go.H * go.W * (C / 8);
     k::ProfScope ps(k::F_EW_BF16, 0, (in_lo_off ? 4.0 : 2.0) * C * ((double)gi.N * gi.H * gi.W + (double)go.N * go.H * go.W), st);
-    maxpool_nhwc_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, in_ctot, c0, C / 8, gi.N, gi.H, gi.W, out, go.H, go.W, arg, in_lo_off, out_lo_off);
+    k::launch_pdl(maxpool_nhwc_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, in, in_ctot, c0, C / 8, gi.N, gi.H, gi.W, out, go.H, go.W, arg, in_lo_off, out_lo_off);
     k::count_launch();
 }
 

@@ -158,6 +158,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(L.tmem_cols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
+    // everything above touched only shared memory and TMEM: from here on the predecessor's results are needed (kcommon.cuh)
+    k::pdl_enter();
     if (warp >= 2) {  // per-channel epilogue parameters
         for (int co = threadIdx.x - 64; co < L.npad_total; co += kEpiThreads) {
             const bool in = co < L.cout;
@@ -731,7 +733,7 @@ static void launch_conv_t(const ConvLaunch& L, cudaStream_t st, int rev)
         attr_set = true;
     }
     const long long items = L.grid_x * (L.npad_total / L.nblk);
-    conv_tc_kernel<NTAPS, KS><<<(unsigned)std::min<long long>(items, k::num_sms()), kThreads, L.smem_bytes, st>>>(L, rev);
+    k::launch_pdl(conv_tc_kernel<NTAPS, KS>, dim3((unsigned)std::min<long long>(items, k::num_sms())), dim3(kThreads), (size_t)L.smem_bytes, st, L, rev);
 }
 
 template <int NTAPS>

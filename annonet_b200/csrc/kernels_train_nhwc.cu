@@ -133,6 +133,7 @@ __device__ __forceinline__ void lds8(const float* p, float f[8])
 __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restrict__ z, int ctot, int c0, long long npos, int mish_first,
                                                             double* __restrict__ sums, int rev)
 {
+    k::pdl_enter();
     const int C8 = blockDim.x;
     float acc[2][8] = {};
     const long long stride = (long long)gridDim.x * blockDim.y;
@@ -167,6 +168,7 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
                                                             const float* __restrict__ beta, const float* __restrict__ stats,
                                                             const BnFinalize fin, int rev)
 {
+    k::pdl_enter();
     __shared__ __align__(16) float s_sc[kMaxC], s_sh[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
     if (fin.sums) {
@@ -244,6 +246,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_reduce_kernel(const float* __
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                  const float* __restrict__ stats, double* __restrict__ red, int rev)
 {
+    k::pdl_enter();
     __shared__ __align__(16) float s_i[kMaxC], s_m[kMaxC], s_g[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
     for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
@@ -308,6 +311,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
                                                                 const double* __restrict__ red, float invnum, float* __restrict__ dgamma,
                                                                 float* __restrict__ dbeta, float* __restrict__ dbias, int rev, float unscale)
 {
+    k::pdl_enter();
     __shared__ __align__(16) float s_k1[kMaxC], s_k2[kMaxC], s_k3[kMaxC], s_a[kMaxC], s_b[kMaxC];
     const int C = blockDim.x * 8, c = threadIdx.x * 8;
     for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < C; i += blockDim.x * blockDim.y) {
@@ -372,6 +376,7 @@ __global__ void __launch_bounds__(kMaxT, 3) bn_bwd_apply_kernel(const float* __r
 __global__ void __launch_bounds__(kMaxT) channel_sum_kernel(const h16* __restrict__ v, int ctot, int c0, long long npos, float* __restrict__ out,
                                                             float unscale)
 {
+    k::pdl_enter();
     float acc[1][8] = {};
     for (long long pos = (long long)blockIdx.x * blockDim.y + threadIdx.y; pos < npos; pos += (long long)gridDim.x * blockDim.y) {
         float f[8];
@@ -391,6 +396,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restr
                                                           const h16* __restrict__ gout, int Ho, int Wo, h16* __restrict__ gin, int gin_ctot,
                                                           int gin_c0)
 {
+    k::pdl_enter();
     const long long total = (long long)N * Hi * Wi * C8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
@@ -450,6 +456,7 @@ __global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __res
 __global__ void __launch_bounds__(256) upsample_zero_kernel(const h16* __restrict__ in, int in_ctot, int in_c0, int C8, int N, int h, int w,
                                                             h16* __restrict__ out)
 {
+    k::pdl_enter();
     const int Hf = 2 * h + 1, Wf = 2 * w + 1;
     const long long total = (long long)N * Hf * Wf * C8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -540,13 +547,13 @@ Shape channel_shape(int C, long long npos, int ctas_per_sm = 8)
 
 }  // namespace
 
-void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev)
+void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev, int pre_zeroed)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 3.0 * g.N * g.H * g.W * z.C, 2.0 * g.N * g.H * g.W * z.C, st);
-    cudaMemsetAsync(sums, 0, sizeof(double) * 2 * z.C, st);
+    if (!pre_zeroed) cudaMemsetAsync(sums, 0, sizeof(double) * 2 * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 4);
-    bn_stats_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, d.total, mish_first, sums, rev);
+    k::launch_pdl(bn_stats_kernel, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, d.total, mish_first, sums, rev);
     k::count_launch();
 }
 
@@ -556,18 +563,18 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, (y.lo_off ? 8.0 : 6.0) * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 4);
-    bn_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
+    k::launch_pdl(bn_apply_kernel, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
     k::count_launch();
 }
 
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
-                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev)
+                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev, int pre_zeroed)
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 6.0 * g.N * g.H * g.W * z.C, 4.0 * g.N * g.H * g.W * z.C, st);
-    cudaMemsetAsync(red, 0, sizeof(double) * 2 * z.C, st);
+    if (!pre_zeroed) cudaMemsetAsync(red, 0, sizeof(double) * 2 * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 3);
-    bn_bwd_reduce_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, d.total, mish_first, has_mish, gamma, beta, stats,
+    k::launch_pdl(bn_bwd_reduce_kernel, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, d.total, mish_first, has_mish, gamma, beta, stats,
                                                      red, rev);
     k::count_launch();
 }
@@ -580,7 +587,7 @@ void bn_backward_apply_nhwc(const ViewF& z, const View& gy, const View& dz, cons
     k::ProfScope ps(k::F_EW_BF16, 8.0 * g.N * g.H * g.W * z.C, 6.0 * g.N * g.H * g.W * z.C, st);
     const Shape s = channel_shape(z.C, d.total, 3);
     const float invnum = 1.0f / (float)((long long)g.N * g.H * g.W);
-    bn_bwd_apply_kernel<<<s.grid, s.block, 0, st>>>(z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, dz.p, dz.ctot, dz.c0, d, mish_first, has_mish, gamma, beta, stats, red,
+    k::launch_pdl(bn_bwd_apply_kernel, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, gy.p, gy.ctot, gy.c0, dz.p, dz.ctot, dz.c0, d, mish_first, has_mish, gamma, beta, stats, red,
                                                     invnum, dgamma, dbeta, dbias, rev, unscale);
     k::count_launch();
 }
@@ -590,7 +597,7 @@ void channel_sum_nhwc(const View& v, const Geo& g, float* out, cudaStream_t st, 
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 1.0 * g.N * g.H * g.W * v.C, 2.0 * g.N * g.H * g.W * v.C, st);
     const Shape s = channel_shape(v.C, d.total);
-    channel_sum_kernel<<<s.grid, s.block, 0, st>>>(v.p, v.ctot, v.c0, d.total, out, unscale);
+    k::launch_pdl(channel_sum_kernel, s.grid, s.block, 0, st, v.p, v.ctot, v.c0, d.total, out, unscale);
     k::count_launch();
 }
 
@@ -599,7 +606,7 @@ void maxpool_backward_nhwc(const uint8_t* arg, int C, const Geo& gi, const h16* 
     const long long n = (long long)gi.N * gi.H * gi.W * (C / 8);
     if (n >= (1ll << 31) * 8) throw std::invalid_argument("maxpool_backward_nhwc: tensor too large");
     k::ProfScope ps(k::F_EW_BF16, 0, 2.0 * C * (2.0 * gi.N * gi.H * gi.W + 1.5 * (double)go.N * go.H * go.W), st);
-    maxpool_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(arg, C / 8, gi.N, gi.H, gi.W, gout_dense, go.H, go.W, gin.p, gin.ctot, gin.c0);
+    k::launch_pdl(maxpool_bwd_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, arg, C / 8, gi.N, gi.H, gi.W, gout_dense, go.H, go.W, gin.p, gin.ctot, gin.c0);
     k::count_launch();
 }
 
@@ -617,7 +624,7 @@ void upsample_zero_nhwc(const View& in, const Geo& gc, h16* out, const Geo& gf, 
     if (gf.H != 2 * gc.H + 1 || gf.W != 2 * gc.W + 1) throw std::logic_error("upsample_zero_nhwc: geometry mismatch");
     const long long n = (long long)gf.N * gf.H * gf.W * (in.C / 8);
     k::ProfScope ps(k::F_PACK, 0, 2.0 * in.C * ((double)gc.N * gc.H * gc.W + (double)gf.N * gf.H * gf.W), st);
-    upsample_zero_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in.p, in.ctot, in.c0, in.C / 8, gc.N, gc.H, gc.W, out);
+    k::launch_pdl(upsample_zero_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, in.p, in.ctot, in.c0, in.C / 8, gc.N, gc.H, gc.W, out);
     k::count_launch();
 }
 

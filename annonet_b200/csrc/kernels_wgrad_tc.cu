@@ -112,6 +112,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(L.tmem_cols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
+    k::pdl_enter();   // shared memory and TMEM only above; the operands (and the scratch the previous reduce still reads) below
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -210,6 +211,7 @@ __global__ void __launch_bounds__(32 * kRL) wgrad_tc_reduce_kernel(const float* 
                                                                    float* __restrict__ out, long long sy, long long sx, float unscale, int t0,
                                                                    int t1, int t2, int t3, int t4, int t5, int t6, int t7, int t8)
 {
+    k::pdl_enter();
     const int tapmap[9] = {t0, t1, t2, t3, t4, t5, t6, t7, t8};
     __shared__ float sh[kRL][33];
     const int ox = threadIdx.x & 31, sl = threadIdx.x >> 5;
@@ -357,10 +359,10 @@ void launch_wgrad_tc(const WgradTcLaunch& L, cudaStream_t st)
         attr_set = true;
     }
     k::ProfScope ps(k::F_WGRAD_TC, L.flops, L.bytes, st);
-    wgrad_tc_kernel<<<dim3(L.nsplit, L.cxtiles), kWThreads, L.smem_bytes, st>>>(L);
+    k::launch_pdl(wgrad_tc_kernel, dim3(L.nsplit, L.cxtiles), dim3(kWThreads), (size_t)L.smem_bytes, st, L);
     const long long total = (long long)L.ntaps * L.cy_real * L.cx_real;
     static const int rl = getenv("AB_RL") ? atoi(getenv("AB_RL")) : 4;   // split lanes per 32 outputs: 4 measured best (2: 7.88, 4: 7.85, 8: 7.88, 16: 7.98, 32: 8.47 ms per step)
-#define AB_REDUCE(R) wgrad_tc_reduce_kernel<R><<<(unsigned)((total + 31) / 32), 32 * R, 0, st>>>(L.scratch, L.nsplit, L.cxtiles, L.ntaps, L.cy_real, L.cx_real, L.out, \
+#define AB_REDUCE(R) k::launch_pdl(wgrad_tc_reduce_kernel<R>, dim3((unsigned)((total + 31) / 32)), dim3(32 * R), 0, st, L.scratch, L.nsplit, L.cxtiles, L.ntaps, L.cy_real, L.cx_real, L.out, \
         L.sy, L.sx, L.unscale, L.tapmap[0], L.tapmap[1], L.tapmap[2], L.tapmap[3], L.tapmap[4], L.tapmap[5], L.tapmap[6], L.tapmap[7], L.tapmap[8])
     if (rl == 2) AB_REDUCE(2); else if (rl == 16) AB_REDUCE(16); else if (rl == 8) AB_REDUCE(8); else AB_REDUCE(4);
 #undef AB_REDUCE

@@ -162,7 +162,9 @@ struct ViewF {   // same, fp32 elements (the conv outputs z that feed a batch no
 };
 // sums[c] = sum x, sums[C + c] = sum x^2 over all positions of x = mish_first ? mish(z) : z (pads are zero and add nothing)
 // rev (all bn passes): walk the positions downwards, so that a pass starts where its producer stopped (L2 reuse)
-void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev = 0);
+// pre_zeroed: `sums` / `red` already holds zeros (the engine clears every layer's slot with ONE memset per step: a memset node
+// in front of each launch would cut the programmatic launch dependency, kcommon.cuh)
+void bn_stats_nhwc(const ViewF& z, const Geo& g, int mish_first, double* sums, cudaStream_t st, int rev = 0, int pre_zeroed = 0);
 // y = mish_first ? gamma*(mish(z)-mean)*invstd+beta : mish(gamma*(z-mean)*invstd+beta)   [mish optional]; pads are left alone
 // Optional fused bn_finalize (kernels_bn.cu): every CTA derives mean / invstd from the layer's sums itself, CTA 0 also
 // updates the running statistics, the saved stats and the device-side num_updates counter (layers.h:1392-1397).
@@ -178,7 +180,7 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
                    const float* stats, cudaStream_t st, const BnFinalize* fin = nullptr, int rev = 0);
 // backward pass 1 (cpu_dlib.cpp:1228-1250): red[c] = sum dv, red[C + c] = sum dv*xhat
 void bn_backward_reduce_nhwc(const ViewF& z, const View& gy, const Geo& g, int mish_first, int has_mish, const float* gamma,
-                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev = 0);
+                             const float* beta, const float* stats, double* red, cudaStream_t st, int rev = 0, int pre_zeroed = 0);
 // backward pass 2 (cpu_dlib.cpp:1252-1288): dz = gradient at the conv output (h16, pads untouched), dgamma/dbeta from `red`,
 // dbias[c] = sum dz (assign_conv_bias_gradient, cpu_dlib.cpp:470-504; dbias must be zeroed by the caller).  gy and dz carry
 // the loss scale; the three parameter gradients are multiplied by `unscale` = 1 / loss scale

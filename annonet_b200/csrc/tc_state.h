@@ -62,6 +62,7 @@ struct TcState {
     DevBuf dpool;              // per transition_down group: gradient at the pooled tensor              [positions][cin]
     DevBuf upx;                // per `up` group: zero-stuffed input on the fine grid (filter gradient)  [positions][cin]
     DevBuf glogits16;          // loss gradient as h16 [positions][8]
+    size_t sums_slot = 0;   // doubles per (layer, pass) slot of `sums`
     DevBuf sums, sums_side, bias_tmp, wscratch, pack_jobs;   // sums_side: batch-statistics scratch of the side stream (dead layers)
     int n_pack_jobs = 0, n_fwd_jobs = 0, max_pack_elems = 0;
     bool train_ready = false;
