@@ -158,7 +158,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(L.tmem_cols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    // everything above touched only shared memory and TMEM: from here on the predecessor's results are needed (kcommon.cuh)
+    if (warp == 0 && lane == 0) {   // the TMA descriptors live in the kernel parameters: fetch them while the predecessor drains
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&L.tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&L.tmB)) : "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // everything above touched only shared memory, TMEM and the kernel parameters: from here on the predecessor's results are
+    // needed (kcommon.cuh).  The TMA and MMA warps start at once; the epilogue warps stage their per-channel parameters behind
+    // a barrier of their own.
     k::pdl_enter();
     if (warp >= 2) {  // per-channel epilogue parameters
         for (int co = threadIdx.x - 64; co < L.npad_total; co += kEpiThreads) {
@@ -167,10 +176,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
             s_scale[co] = (in && L.act != ACT_NONE) ? __ldg(L.scale + co) : 1.f;
             s_shift[co] = (in && L.act != ACT_NONE) ? __ldg(L.shift + co) : 0.f;
         }
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
     }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = tmem_base_slot;
 
     if (warp == 0) {
