@@ -82,12 +82,6 @@ __device__ __forceinline__ void tmem_ld_fence(float v[16])
                       "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]) :: "memory");
 }
 
-// p[0..7] += v[0..7] (fp16, round to nearest) as one 16-byte reduction performed at the L2; p is 16-byte aligned
-__device__ __forceinline__ void red_add_h8(h16* p, const uint32_t v[4])
-{
-    asm volatile("red.global.add.noftz.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
-}
-
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, LBO (unused for
 // swizzled K-major) = 1, SBO = 8 rows * pitch, version 1, layout type 6/4/2 for 32/64/128-byte swizzle.
 __device__ __forceinline__ uint64_t smem_desc_hi(int pitch)

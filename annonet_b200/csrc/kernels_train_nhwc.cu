@@ -428,11 +428,8 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const uint8_t* __restr
         }
     if (!any) return;
     h16* gp = gin + (n * Si + (long long)(y + 1) * (Wi + 1) + (x + 1)) * gin_ctot + gin_c0 + cg * 8;
-    float old[8];
-    unpack8(ld8(gp), old);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) old[k] += acc[k];
-    st8(gp, pack8(old));
+    const BF8 a = pack8(acc);   // one 16-byte reduction at the L2 instead of load + add + store (h16.cuh)
+    red_add_h8(gp, reinterpret_cast<const uint32_t*>(a.v));
 }
 
 __global__ void __launch_bounds__(256) planes_to_nhwc8_kernel(const float* __restrict__ planes, int K, h16* __restrict__ out, int N, int H, int W,

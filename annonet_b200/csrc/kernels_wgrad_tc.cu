@@ -112,10 +112,10 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_tc_kernel(const __grid_con
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(L.tmem_cols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    k::pdl_enter();   // shared memory and TMEM only above; the operands (and the scratch the previous reduce still reads) below
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    k::pdl_enter();   // shared memory and TMEM only above; the operands (and the scratch the previous reduce still reads) below
     const uint32_t tmem = tmem_base_slot;
 
     if (warp == 0) {
