@@ -16,7 +16,7 @@ struct Reader {
     Reader(const void* b, size_t n_) : p((const unsigned char*)b), n(n_) {}
 
     void need(size_t k) const {
-        if (pos + k > n) throw serialization_error("unexpected end of the serialized net at byte " + std::to_string(pos));
+        if (k > n - pos) throw serialization_error("unexpected end of the serialized net at byte " + std::to_string(pos));   // (pos <= n always: no overflow)
     }
     long long integer() {  // serialize.h:297-345 (+ unpack_int :347-420)
         need(1);
@@ -55,8 +55,14 @@ struct Reader {
     void tensor(HostTensor& t) {  // cuda/tensor.h:444-466
         if (integer() != 2) throw serialization_error("unexpected tensor version at " + std::to_string(pos));
         for (int i = 0; i < 4; ++i) t.d[i] = integer();
-        const long long cnt = t.d[0] * t.d[1] * t.d[2] * t.d[3];
-        if (cnt < 0) throw serialization_error("negative tensor size");
+        // every dimension is checked before the product: a hostile stream must not overflow it (or pass a negative pair)
+        unsigned long long cnt = 1;
+        for (int i = 0; i < 4; ++i) {
+            if (t.d[i] < 0) throw serialization_error("negative tensor dimension at " + std::to_string(pos));
+            if (t.d[i] != 0 && cnt > (unsigned long long)(n / 4) / (unsigned long long)t.d[i])
+                throw serialization_error("tensor larger than the serialized net at " + std::to_string(pos));
+            cnt *= (unsigned long long)t.d[i];
+        }
         need((size_t)cnt * 4);
         t.v.resize((size_t)cnt);
         if (cnt) std::memcpy(t.v.data(), p + pos, (size_t)cnt * 4);

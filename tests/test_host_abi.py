@@ -46,6 +46,31 @@ def test_cpp_codec_rejects_garbage(ab):
         ab.transcode(b"\x01\x01\x01\x05hello")
 
 
+def test_cpp_codec_rejects_hostile_tensor_headers(ab, monkeypatch):
+    """a tensor header whose dimensions are negative in pairs, or whose product wraps around 64 bits, must end in a
+    serialization error -- not in a huge allocation or a read past the buffer"""
+    import dlib_format as df
+    net = df.parse_net(golden_bytes("anet_small_trained.dnn"))
+    orig = df.Writer.tensor
+    for dims in ((-1, -1, 4, 4), (1 << 31, 1 << 31, 4, 1), (1 << 40, 1 << 20, 1, 1), (1 << 62, 1, 1, 1), (3, -2, 1, 1)):
+        state = {"done": False}
+
+        def hostile(self, a, dims=dims, state=state):
+            if a is not None and a.size and not state["done"]:
+                state["done"] = True
+                self.int(2)
+                for d in dims:
+                    self.int(d)
+                return None
+            return orig(self, a)
+        monkeypatch.setattr(df.Writer, "tensor", hostile)
+        data = df.serialize_net(net)
+        monkeypatch.setattr(df.Writer, "tensor", orig)
+        assert state["done"]
+        with pytest.raises(ab.SerializationError):
+            ab.transcode(data)
+
+
 def test_tiles_match_reference(ab):
     t = golden_json("tiles.json")
     for key, rows in t["tiles"].items():
