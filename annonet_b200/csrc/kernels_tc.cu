@@ -573,7 +573,20 @@ void make_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int
 
 void make_tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int ctot, int box_ch, int box_rows)
 {
-    make_map_2d(m, base, rows, ctot, box_ch, box_rows, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    // L2 promotion of the TMA fetches.  A box row is box_ch * 2 bytes of a ctot * 2-byte row: for the narrow channel slices of the
+    // full-resolution levels (32 of 160 bytes) a 128-byte promotion fetches neighbours nobody asked for.  AB_TMA_PROMO: 0 none,
+    // 1 64 B, 2 128 B, 3 256 B, 4 (default) = the smallest promotion covering the box row.
+    static const int promo_env = getenv("AB_TMA_PROMO") ? atoi(getenv("AB_TMA_PROMO")) : 2;
+    CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    const int row_bytes = box_ch * 2;
+    switch (promo_env) {
+        case 0: promo = CU_TENSOR_MAP_L2_PROMOTION_NONE; break;
+        case 1: promo = CU_TENSOR_MAP_L2_PROMOTION_L2_64B; break;
+        case 3: promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B; break;
+        case 4: promo = row_bytes <= 32 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : row_bytes <= 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B; break;
+        default: break;
+    }
+    make_map_2d(m, base, rows, ctot, box_ch, box_rows, promo);
 }
 
 int padded_n(int cout) { return (cout + 15) / 16 * 16; }
@@ -720,8 +733,11 @@ void setup_conv(ConvLaunch& L, const ConvSetup& s)
         fprintf(stderr, "tc conv: P %d cin %d npad %d taps %d -> kc %d %s th %d nseg %d seg %d stages %d smem %u ctas %lld cost %.1f\n", P, s.cin,
                 s.npad_total, s.ntaps, L.kc, L.kym ? "KYM" : L.rows_mode ? "ROWS" : "FLAT", L.th, L.nseg, L.seg_alloc, L.stages, L.smem_bytes, best.ctas, best.cost);
     // activations: 64-byte L2 promotion -- a narrow channel slice costs 64 B of HBM traffic per position instead of 128 (experiments/tma_bench.cu)
-    make_map_2d(&L.tmA, s.src, s.src_positions * (s.split ? 2 : 1), s.src_ctot, L.kc, L.box_rows,
-                L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+    static const int promo_env = getenv("AB_TMA_PROMO") ? atoi(getenv("AB_TMA_PROMO")) : 2;   // (see make_tensor_map_2d)
+    CUtensorMapL2promotion promoA = L.kc * 2 < 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    if (promo_env == 0) promoA = CU_TENSOR_MAP_L2_PROMOTION_NONE;
+    if (promo_env == 4 && L.kc * 2 <= 32) promoA = CU_TENSOR_MAP_L2_PROMOTION_NONE;
+    make_map_2d(&L.tmA, s.src, s.src_positions * (s.split ? 2 : 1), s.src_ctot, L.kc, L.box_rows, promoA);
     make_map_2d(&L.tmB, s.packed, (long long)s.ntaps * npad_total, padded_k(s.cin), L.kc, L.nblk, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
 }
 

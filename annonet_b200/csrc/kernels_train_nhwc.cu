@@ -163,7 +163,8 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_stats_kernel(const float* __restr
 }
 
 // y = mish_first ? mish(z)*sc + sh : mish(z*sc + sh),   sc = gamma*invstd, sh = beta - mean*sc
-__global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, h16* __restrict__ y, int y_ctot,
+template <int U>
+__global__ void __launch_bounds__(kMaxT, U == 2 ? 4 : 3) bn_apply_kernel(const float* __restrict__ z, int z_ctot, int z_c0, h16* __restrict__ y, int y_ctot,
                                                             int y_c0, long long y_lo, GeoD g, int mish_first, int has_mish, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, const float* __restrict__ stats,
                                                             const BnFinalize fin, int rev)
@@ -208,11 +209,11 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
     }
     __syncthreads();
     const long long stride = (long long)gridDim.x * blockDim.y;
-    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < g.total; p0 += kU * stride) {
-        float f[kU][8];
-        bool ok[kU];
+    for (long long p0 = (long long)blockIdx.x * blockDim.y + threadIdx.y; p0 < g.total; p0 += U * stride) {
+        float f[U][8];
+        bool ok[U];
 #pragma unroll
-        for (int u = 0; u < kU; ++u) {
+        for (int u = 0; u < U; ++u) {
             const long long q = p0 + u * stride, pos = rev ? g.total - 1 - q : q;
             ok[u] = q < g.total && is_pixel(g, pos);
             if (ok[u]) ldf8(z + pos * z_ctot + z_c0 + c, f[u]);
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(kMaxT, 4) bn_apply_kernel(const float* __restr
         lds8(s_sc + c, sc);
         lds8(s_sh + c, sh);
 #pragma unroll
-        for (int u = 0; u < kU; ++u) {
+        for (int u = 0; u < U; ++u) {
             if (!ok[u]) continue;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -559,8 +560,16 @@ void bn_apply_nhwc(const ViewF& z, const View& y, const Geo& g, int mish_first, 
 {
     const GeoD d = geod(g);
     k::ProfScope ps(k::F_EW_BF16, 4.0 * g.N * g.H * g.W * z.C, (y.lo_off ? 8.0 : 6.0) * g.N * g.H * g.W * z.C, st);
-    const Shape s = channel_shape(z.C, d.total, 4);
-    k::launch_pdl(bn_apply_kernel, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
+    // positions per thread and loop iteration: ncu on the level-0 layers shows the kernel waiting on memory (17 warps stalled on the
+    // long scoreboard per issue, 33 % issue activity), yet four positions per thread at 3 CTAs per SM are no faster than two at 4
+    static const int unroll = getenv("AB_BN_U") ? atoi(getenv("AB_BN_U")) : 2;   // measured: 2 -> 7.96, 4 -> 7.98 ms per step
+    if (unroll == 2) {
+        const Shape s = channel_shape(z.C, d.total, 4);
+        k::launch_pdl(bn_apply_kernel<2>, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
+    } else {
+        const Shape s = channel_shape(z.C, d.total, 3);
+        k::launch_pdl(bn_apply_kernel<4>, s.grid, s.block, 0, st, z.p, z.ctot, z.c0, y.p, y.ctot, y.c0, y.lo_off, d, mish_first, has_mish, gamma, beta, stats, fin ? *fin : BnFinalize{}, rev);
+    }
     k::count_launch();
 }
 
