@@ -45,10 +45,12 @@ __device__ __forceinline__ BF8 ld8(const h16* p)
     asm volatile("ld.global.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "l"(p));
     return r;
 }
+// 8 floats = one 32-byte sector in ONE load (LDG.E.256, sm_100): as two 16-byte loads every sector was requested twice (ncu on
+// bn_apply: "16 of the 32 bytes per sector used per thread").  p is 32-byte aligned: rows and slices are multiples of 8 floats.
 __device__ __forceinline__ void ldf8(const float* p, float f[8])
 {
-    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(f[0]), "=f"(f[1]), "=f"(f[2]), "=f"(f[3]), "=f"(f[4]), "=f"(f[5]), "=f"(f[6]), "=f"(f[7]) : "l"(p));
 }
 // one 16-byte store (a struct copy of BF8 is emitted member by member: four 4-byte stores -- seen in the SASS of bn_apply)
 __device__ __forceinline__ void st8(h16* p, const BF8& v)
