@@ -145,7 +145,13 @@ def synthetic_batch(n, h, w, k, seed):
 # ---- the reference's own CPU implementation (oracle/_ref/annonet_ref: unmodified dlib CPU build) --------------
 def _ref(*args, timeout=3000):
     env = dict(os.environ)
-    env.setdefault("OMP_NUM_THREADS", str(os.cpu_count() or 1))
+    # all the host threads it can use: torchrun exports OMP_NUM_THREADS=1 for its workers, which would pin the reference's OpenMP
+    # loops to one core (AB_REF_THREADS overrides)
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    env["OMP_NUM_THREADS"] = os.environ.get("AB_REF_THREADS", str(avail))
     r = subprocess.run([REF_BIN, *map(str, args)], check=True, capture_output=True, text=True, timeout=timeout, env=env)
     return r.stdout
 
