@@ -2,6 +2,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <stdexcept>
 
 namespace ab {
@@ -84,23 +85,69 @@ int band_input_dimension(int minimum, int levels)
 }
 }  // namespace
 
-// Tiles arrive row by row (tiling.cpp:57-83).  Rows are dealt to the ranks as contiguous bands of near-equal COST (the
-// pixels the net actually runs: every tile is enlarged to 64k + 63) -- not round-robin: neighbouring rows share a seam, so
-// a band exchanges at most two seams, and 19 rows over 8 ranks cost max 3 rows either way but far less traffic.
+// Tiles arrive row by row (tiling.cpp:57-83).  Each rank gets a contiguous run of them -- a BAND -- of near-equal COST (the pixels
+// the net actually runs: every tile is enlarged to 64k + 63); neighbouring bands share a seam, so a band talks to at most two
+// others.  Every image row is owned (argmax) by exactly one rank.
+//
+// Tile granularity (the default where it applies): a band may begin and end in the middle of a tile row.  A split row is OWNED
+// by the rank that holds its first tile; the other rank sends what its tiles of that row added -- the whole row's strip, not just
+// the 127-row overlap -- to the owner through the same strip exchange.  That is a few hundred MB over NVLink against whole
+// tiles of compute, and it takes the balance from "19 rows over 8 ranks = 3 rows on the busiest against 2.375 on average" to
+// within one tile.  The exchange stays with the two neighbours as long as every band contains at least one whole tile row
+// (then the rows above and below a split row are owned by the two ranks that split it); where that does not hold -- few rows
+// per rank -- or with AB_BAND_ROWS=1 the bands are whole rows as before.
+static bool plan_bands_by_tile(const std::vector<Tile>& tiles, const std::vector<int>& row_start, const std::vector<double>& cost, int world,
+                               std::vector<Band>& bands)
+{
+    const int rows = (int)row_start.size() - 1, ntiles = (int)tiles.size();
+    if (world < 2 || ntiles < world) return false;
+    double total = 0;
+    for (double c : cost) total += c;
+    std::vector<int> cut(world + 1, 0);
+    cut[world] = ntiles;
+    int j = 0;
+    double done = 0;
+    for (int r = 1; r < world; ++r) {   // the cut whose cumulative cost is closest to r / world of the total
+        const double target = total * r / world;
+        while (j < ntiles && std::abs(done + cost[j] - target) <= std::abs(done - target)) done += cost[j++];
+        cut[r] = j;
+    }
+    auto row_of = [&](int tile) { return (int)(std::upper_bound(row_start.begin(), row_start.end(), tile) - row_start.begin()) - 1; };
+    for (int r = 0; r < world; ++r) {
+        if (cut[r + 1] <= cut[r]) return false;
+        // first row that STARTS inside the band, and the row of its last tile
+        const int first_row = row_of(cut[r]) + (row_start[row_of(cut[r])] == cut[r] ? 0 : 1), last_row = row_of(cut[r + 1] - 1);
+        // a whole row inside the band: starts at or after the band's first tile and ends at or before its last
+        bool whole = false;
+        for (int q = first_row; q <= last_row && q < rows; ++q) whole = whole || (row_start[q] >= cut[r] && row_start[q + 1] <= cut[r + 1]);
+        if (!whole || first_row > last_row) return false;
+        Band& b = bands[r];
+        b.t0 = cut[r]; b.t1 = cut[r + 1];
+        b.own0 = tiles[row_start[first_row]].non_overlapping[1];      // rows it owns: from its first whole row ...
+        b.own1 = tiles[b.t1 - 1].non_overlapping[3];                  // ... to the row of its last tile (a split row goes to its first holder)
+        b.f0 = tiles[b.t0].full[1]; b.f1 = tiles[b.t1 - 1].full[3];
+    }
+    return true;
+}
+
 std::vector<Band> plan_bands(const std::vector<Tile>& tiles, int world, int levels)
 {
     std::vector<int> row_start;   // first tile of each tile row
-    std::vector<double> row_cost;
+    std::vector<double> row_cost, tile_cost(tiles.size());
     for (size_t i = 0; i < tiles.size(); ++i) {
         if (i == 0 || tiles[i].full[1] != tiles[i - 1].full[1]) { row_start.push_back((int)i); row_cost.push_back(0); }
         const int fw = tiles[i].full[2] - tiles[i].full[0] + 1, fh = tiles[i].full[3] - tiles[i].full[1] + 1;
-        row_cost.back() += (double)band_input_dimension(fw, levels) * band_input_dimension(fh, levels);
+        tile_cost[i] = (double)band_input_dimension(fw, levels) * band_input_dimension(fh, levels);
+        row_cost.back() += tile_cost[i];
     }
     const int rows = (int)row_start.size();
     row_start.push_back((int)tiles.size());
     double total = 0;
     for (double c : row_cost) total += c;
     std::vector<Band> bands(world);
+    static const bool rows_only = getenv("AB_BAND_ROWS") && atoi(getenv("AB_BAND_ROWS")) != 0;
+    if (!rows_only && plan_bands_by_tile(tiles, row_start, tile_cost, world, bands)) return bands;
+    bands.assign(world, Band{});
     int j = 0;
     double done = 0;
     for (int r = 0; r < world; ++r) {

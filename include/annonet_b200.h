@@ -127,9 +127,9 @@ ab_status ab_process(ab_net* net, const uint8_t* image_hwc, int h, int w, const 
 ab_status ab_get_tiles(int width, int height, int max_tile_w, int max_tile_h, int overlap_x, int overlap_y,
                        ab_tile* out, int cap, int* count);
 
-/* The band plan of a sharded annonet_infer() (host only; what ab_infer_tiled does after ab_comm_init): the tile rows of
+/* The band plan of a sharded annonet_infer() (host only; what ab_infer_tiled does after ab_comm_init): the tiles of
  * ab_get_tiles(width, height, ...) with overlap 2^(levels+1)-1 are dealt to `world` ranks as contiguous bands of near-equal
- * cost.  out: world x 6 ints {first tile, one past the last tile, first/last image row the rank owns (runs argmax on),
+ * cost (a band may begin and end inside a tile row where every band still holds a whole row; AB_BAND_ROWS=1: whole rows only).  out: world x 6 ints {first tile, one past the last tile, first/last image row the rank owns (runs argmax on),
  * first/last image row its tiles touch (extent of its private canvas)}; an empty band has first tile == last tile. */
 ab_status ab_plan_bands(int width, int height, int max_tile_w, int max_tile_h, int levels, int world, int* out);
 

@@ -103,27 +103,80 @@ def test_sharded_inference_and_gradient_exchange_world2(tmp_path):
     assert np.allclose(got["gsum"] / 2, got["gmean"], rtol=0, atol=1e-6)
 
 
+def _tile_cost(t):
+    fw, fh = t["full"][2] - t["full"][0] + 1, t["full"][3] - t["full"][1] + 1
+    return on.recommended_input_dimension(fw, 6) * on.recommended_input_dimension(fh, 6)
+
+
 def test_bands_partition_the_tiles_and_the_rows():
     import annonet_b200 as ab
-    for (w, h, tile) in ((W, H, TILE), (16384, 16384, 1024), (300, 5000, 256), (200, 200, 512)):
+    for (w, h, tile) in ((W, H, TILE), (16384, 16384, 1024), (300, 5000, 256), (200, 200, 512), (2200, 2200, 256)):
         tiles = on.get_tiles(w, h, tile, tile, 127, 127)
         assert tiles == ab.get_tiles(w, h, tile, tile, 127, 127)
         tops = sorted({t["full"][1] for t in tiles})
-        cost = {}
-        for t in tiles:
-            fw, fh = t["full"][2] - t["full"][0] + 1, t["full"][3] - t["full"][1] + 1
-            cost[t["full"][1]] = cost.get(t["full"][1], 0) + on.recommended_input_dimension(fw, 6) * on.recommended_input_dimension(fh, 6)
+        cost = [_tile_cost(t) for t in tiles]
+        row_cost = {}
+        for t, c in zip(tiles, cost):
+            row_cost[t["full"][1]] = row_cost.get(t["full"][1], 0) + c
         for world in (1, 2, 3, 4, 8):
             bands = ab.plan_bands(w, h, tile, tile, world)
             live = [b for b in bands if b["t1"] > b["t0"]]
-            assert len(live) == min(world, len(tops))                       # nobody idles while there are rows to deal
+            assert len(live) == min(world, len(tops)) or len(live) == world      # nobody idles while there is work to deal
             assert live[0]["t0"] == 0 and live[-1]["t1"] == len(tiles)
             assert all(a["t1"] == b["t0"] for a, b in zip(live, live[1:]))  # contiguous, in order
             assert live[0]["own0"] == 0 and live[-1]["own1"] == h - 1
             assert all(a["own1"] + 1 == b["own0"] for a, b in zip(live, live[1:]))   # owned rows tile the image
+            by_row = all(b["t0"] == 0 or tiles[b["t0"]]["full"][1] != tiles[b["t0"] - 1]["full"][1] for b in live)
             for b in live:
                 assert b["f0"] <= b["own0"] <= b["own1"] <= b["f1"]
-                assert tiles[b["t0"]]["full"][1] != tiles[b["t0"] - 1]["full"][1] if b["t0"] else True   # cut between tile rows
-            # balance: no band costs more than the ideal share plus one tile row
-            per = [sum(cost[y] for y in {t["full"][1] for t in tiles[b["t0"]:b["t1"]]}) for b in live]
-            assert max(per) <= sum(cost.values()) / len(live) + max(cost.values()) + 1e-9
+                assert b["f0"] == tiles[b["t0"]]["full"][1] and b["f1"] == tiles[b["t1"] - 1]["full"][3]
+                # a split row belongs to the rank that holds its first tile; every band holds a whole row it owns
+                first_own = next(t for t in tiles[b["t0"]:b["t1"]] if t["non_overlapping"][1] == b["own0"])
+                assert first_own["full"][0] == tiles[0]["full"][0]                     # ... which starts at the left edge
+                assert tiles[b["t1"] - 1]["non_overlapping"][3] == b["own1"]
+                # strips only ever go to the two neighbours: nothing of this band lies above the previous band's rows or below the next's
+                i = live.index(b)
+                if i > 0: assert b["f0"] >= live[i - 1]["own0"]
+                if i + 1 < len(live): assert b["f1"] <= live[i + 1]["own1"]
+            # balance: no band costs more than the ideal share plus one unit of the plan's granularity (a tile, or a tile row)
+            per = [sum(cost[b["t0"]:b["t1"]]) for b in live]
+            unit = max(row_cost.values()) if by_row else max(cost)
+            assert max(per) <= sum(cost) / len(live) + unit + 1e-9
+        if (w, h, tile) in ((16384, 16384, 1024), (2200, 2200, 256)):     # enough rows per rank: the tile-granular plan applies
+            bands = ab.plan_bands(w, h, tile, tile, 8)
+            per = [sum(cost[b["t0"]:b["t1"]]) for b in bands]
+            assert max(per) <= 1.03 * sum(cost) / 8, "8 ranks: busiest band within 3 % of the mean"
+
+
+@pytest.mark.parametrize("world", [2, 3, 5, 8])
+def test_strip_protocol_reproduces_the_one_process_label_map(world):
+    """the engine's protocol for `world` ranks, run in ONE process: private band canvases, strips added at their owners, argmax of
+    the owned rows -- on an image with enough tile rows that bands begin and end in the middle of a row"""
+    import annonet_b200 as ab
+    h = w = 2200
+    img = np.random.default_rng(11).integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+    anet = df.Net(layers=[{"type": "loss"}, {"type": "con", "num_filters": K}], levels=6)
+    ref_labels, ref_canvas = on.annonet_infer(anet, img, TILE, TILE, return_blended=True, forward_fn=_fake_forward)
+    bands = ab.plan_bands(w, h, TILE, TILE, world)
+    tiles = on.get_tiles(w, h, TILE, TILE, 127, 127)
+    if world == 8:
+        assert any(tiles[b["t0"]]["full"][0] != tiles[0]["full"][0] for b in bands[1:]), "expected bands that start inside a tile row"
+    private = []
+    for b in bands:
+        _, c = on.annonet_infer(anet, img, TILE, TILE, return_blended=True, forward_fn=_fake_forward, tile_range=(b["t0"], b["t1"]))
+        assert not c[:, :b["f0"]].any() and not c[:, b["f1"] + 1:].any()
+        private.append(c)
+    final = [c.copy() for c in private]
+    for r in range(world):
+        sends, recvs = _strips(bands, r)
+        for peer, y0, y1 in sends:
+            assert (r, y0, y1) in _strips(bands, peer)[1], "every send has its matching receive"
+            final[peer][:, y0:y1 + 1] += private[r][:, y0:y1 + 1]
+        for peer, y0, y1 in recvs:
+            assert (r, y0, y1) in _strips(bands, peer)[0], "every receive has its matching send"
+    labels = np.zeros((h, w), np.uint16)
+    for r, b in enumerate(bands):
+        rows = slice(b["own0"], b["own1"] + 1)
+        assert np.max(np.abs(final[r][:, rows] - ref_canvas[:, rows])) <= 1e-5 * np.abs(ref_canvas).max()
+        labels[rows] = on.to_label(final[r][:, rows], ())
+    assert np.mean(labels != ref_labels) < 1e-4
