@@ -226,3 +226,47 @@ def test_f16_loss_scale_is_transparent(ab):
         grads.append(np.concatenate([net.layer_gradient(i) for i, _ in onet.param_layers()]))
     for g in grads[1:]:
         assert _rel_l2(g, grads[0].astype(np.float64)) < 5e-3
+
+
+def test_f16_request_on_a_width_scaled_net_runs_on_the_fp32_kernels(ab):
+    """annonet_train --net-width-scaler gives 4 / 6 / 10-channel layers the tcgen05 kernels cannot take (16-byte channel vectors):
+    a net created with AB_PRECISION_F16 must then train on the fp32 kernels -- same numbers as the fp32 golden run -- not throw"""
+    from conftest import golden_bytes, golden_npz
+    t, gr = golden_npz("train_inputs.npz"), golden_npz("train_grads.npz")
+    net = ab.TrainingNet(0, ab.AB_PRECISION_F16)
+    net.Deserialize(golden_bytes("net_small.dnn"))
+    assert net.info()["precision"] == ab.AB_PRECISION_FP32, "the narrow golden net cannot run on the tensor-core path"
+    loss = net.compute_gradients(t["images"][:3], ab.pack_labels(t["labels"][:3], t["weights"][:3]))
+    assert abs(loss - float(gr["loss"])) < 1e-4 * float(gr["loss"])
+    full = ab.TrainingNet(0, ab.AB_PRECISION_F16)
+    full.Deserialize(df.serialize_net(df.random_net(class_count=3, seed=3)))
+    assert full.info()["precision"] == ab.AB_PRECISION_F16       # (and a full-width net stays on it)
+
+
+def test_f16_training_with_12_classes_follows_the_fp32_path(ab):
+    """more classes than one 8-channel vector of logit gradients (round 1's limit): loss, logits and every layer's gradient of the
+    tensor-core path against the fp32 path of the same engine, which is pinned to the reference at 1e-4"""
+    from conftest import train_case
+    onet = df.random_net(class_count=12, seed=33)
+    data = df.serialize_net(onet)
+    imgs, labs, wts = train_case(4, 191, 191, 12, seed=12)
+    wl = ab.pack_labels(labs, wts)
+    out = {}
+    for name, prec in (("fp32", ab.AB_PRECISION_FP32), ("f16", ab.AB_PRECISION_F16)):
+        net = ab.TrainingNet(0, prec)
+        net.Deserialize(data)
+        assert net.info()["precision"] == prec and net.info()["class_count"] == 12
+        loss = net.compute_gradients(imgs, wl)
+        grads = {i: net.layer_gradient(i) for i, l in enumerate(onet.layers) if l["type"] in ("con", "cont", "bn")}
+        out[name] = (loss, net.logits(), grads)
+    (l32, z32, g32), (l16, z16, g16) = out["fp32"], out["f16"]
+    assert abs(l16 - l32) < 1e-3 * abs(l32), (l16, l32)
+    assert rel_err(z16, z32) < TOL
+    a = np.concatenate([g16[i].ravel() for i in sorted(g32)]).astype(np.float64)
+    b = np.concatenate([g32[i].ravel() for i in sorted(g32)]).astype(np.float64)
+    whole = float(np.linalg.norm(a - b) / np.linalg.norm(b))
+    worst = max(float(np.linalg.norm(g16[i].astype(np.float64) - g32[i]) / np.linalg.norm(g32[i])) for i in g32 if np.abs(g32[i]).max() > 0)
+    print(f"12 classes: loss {l16:.6f} vs {l32:.6f}, logits {rel_err(z16, z32):.2e}, whole gradient rel-L2 {whole:.2e}, worst layer {worst:.2e}")
+    # a 4 x 191 x 191 batch leaves the deepest batch norms 36 samples per channel: the per-layer bar at BASELINE sizes is 2e-2
+    # (test_f16_training_matches_reference_on_baseline_config1); here the point is that 12 classes train on this path at all
+    assert whole < TOL and worst < 1e-1
